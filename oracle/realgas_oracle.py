@@ -43,7 +43,7 @@ AU = 1.495978707e11
 R_sun = 6.96340e8
 T_sun = 5778
 
-_trapz = getattr(np, "trapz", None) or np.trapezoid
+_trapz = getattr(np, "trapezoid", None) or np.trapz
 
 
 # ------------------------------------------------------------------------------------------
