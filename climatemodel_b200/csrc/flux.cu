@@ -1,0 +1,359 @@
+// Host drivers of the flux path: level-table construction, plan-grid optical depth, and the
+// cmb200_flux / cmb200_flux_host entry points (RealGas.get_flux + net flux + heating rate).
+#include <algorithm>
+#include <cstring>
+
+#include "flux_kernels.cuh"
+
+namespace cmb {
+
+static int sm_count(int device) {
+    static int cached[64] = {0};
+    if (device < 64 && cached[device]) return cached[device];
+    int n = 148;
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device);
+    if (device < 64) cached[device] = n;
+    return n;
+}
+
+static int ensure_tidx(cmb200_plan *p, int64_t n_col, const double *T_tau, const double *T_g,
+                       cudaStream_t s) {
+    size_t need = (size_t)p->M * n_col * p->L;
+    if (p->tidx.n < need) CMB_CUDA(p->tidx.alloc(need));
+    for (int m = 0; m < p->M; ++m) {
+        int64_t n = n_col * p->L;
+        tidx_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(T_tau, T_g, n_col, p->L,
+                                                               p->T_axes.p + (size_t)m * p->nT_pad,
+                                                               p->nT_pad, p->tidx.p + (size_t)m * n);
+        CMB_LAUNCHED();
+    }
+    return CMB200_OK;
+}
+
+// Decide how many warps share one column and lay out the partial-sum slots.
+static int ensure_partition(cmb200_plan *p, int64_t n_col, int warps_per_cta) {
+    Partition &pt = p->partition;
+    if (pt.n_col == n_col) return CMB200_OK;
+    const int64_t target = (int64_t)sm_count(p->device) * warps_per_cta * 2;
+    int parts = 1;
+    if (n_col < target) parts = (int)std::min<int64_t>(p->n_seg, (target + n_col - 1) / n_col);
+    if (parts < 1) parts = 1;
+    std::vector<int32_t> seg0(parts + 1), slot0(parts), bslot(p->B + 1, 0);
+    for (int i = 0; i <= parts; ++i) seg0[i] = (int32_t)((int64_t)i * p->n_seg / parts);
+    std::vector<int32_t> slot_band;
+    for (int i = 0; i < parts; ++i) {
+        slot0[i] = (int32_t)slot_band.size();
+        int last = -1;
+        for (int s = seg0[i]; s < seg0[i + 1]; ++s)
+            if (p->hseg_band[s] != last) {
+                last = p->hseg_band[s];
+                slot_band.push_back(last);
+            }
+    }
+    for (int j = 0; j <= p->B; ++j)
+        bslot[j] = (int32_t)(std::lower_bound(slot_band.begin(), slot_band.end(), j) - slot_band.begin());
+    pt.parts = parts;
+    pt.n_slots = (int)slot_band.size();
+    CMB_CUDA(pt.part_seg0.upload(seg0.data(), seg0.size()));
+    CMB_CUDA(pt.part_slot0.upload(slot0.data(), slot0.size()));
+    CMB_CUDA(pt.band_slot0.upload(bslot.data(), bslot.size()));
+    CMB_CUDA(cudaDeviceSynchronize());
+    pt.n_col = n_col;
+    return CMB200_OK;
+}
+
+template <typename Real, bool FUSED>
+static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *Tint, cudaStream_t s) {
+    const int L = p->L;
+    const size_t per_warp = flux_warp_smem<Real, FUSED>(L, p->M);
+    int max_smem = 0;
+    CMB_CUDA(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, p->device));
+    int warps = (int)std::min<size_t>(8, (size_t)max_smem / per_warp);
+    if (warps < 1) {
+        set_error("%d levels need %zu bytes of shared memory per warp; the device offers %d", L, per_warp, max_smem);
+        return CMB200_ERR_LIMIT;
+    }
+    int rc = ensure_partition(p, io->n_col, warps);
+    if (rc) return rc;
+    const Partition &pt = p->partition;
+    if (pt.parts > 1) {
+        size_t need = (size_t)io->n_col * pt.n_slots * 2 * L;
+        if (p->scratch.n < need) CMB_CUDA(p->scratch.alloc(need));
+    }
+    FluxArgs<Real> a;
+    memset(&a, 0, sizeof(a));
+    a.L = L;
+    a.B = p->B;
+    a.M = p->M;
+    a.nT_pad = p->nT_pad;
+    a.parts = pt.parts;
+    a.n_slots = pt.n_slots;
+    a.N = p->N;
+    a.pitch = p->pitch;
+    a.n_col = io->n_col;
+    a.geo = p->geo.p;
+    a.Pint = p->P.p;
+    a.hdP = p->hdP.p;
+    a.band_start = p->band_start.p;
+    a.band_len = p->band_len.p;
+    a.band_centre = p->band_centre.p;
+    a.band_delta = p->band_delta.p;
+    a.band_sumw = p->band_sumw.p;
+    a.band_sw = p->band_sw.p;
+    a.wchain = std::is_same<Real, double>::value ? (const Real *)p->wchain64.p : (const Real *)p->wchain32.p;
+    a.chain_off = p->chain_off.p;
+    a.seg_band = p->seg_band.p;
+    a.seg_c0 = p->seg_c0.p;
+    a.part_seg0 = pt.part_seg0.p;
+    a.part_slot0 = pt.part_slot0.p;
+    a.pc = PlanckConst{p->c.h_planck, p->c.speed_of_light, p->c.k_boltzmann};
+    a.T_star = p->T_star;
+    a.star_geom = p->R_star * p->R_star / (p->dist * p->dist);
+    a.g = p->c.g;
+    a.g_over_cp = p->c.g / p->c.c_p_dry;
+    a.T = io->T;
+    a.Tint = Tint;
+    a.T_g = io->T_g;
+    a.albedo = io->albedo;
+    a.albedo_scalar = io->albedo_scalar;
+    a.tau = io->tau;
+    a.tau_id = io->tau_id;
+    a.KL = std::is_same<Real, double>::value ? (const Real *)p->KL64.p : (const Real *)p->KL32.p;
+    a.tidx = p->tidx.p;
+    a.q = io->q;
+    a.q_col_stride = io->q_per_column ? L : 0;
+    a.q_mol_stride = io->q_per_column ? io->n_col * L : L;
+    a.up = io->up;
+    a.down = io->down;
+    a.net = io->net;
+    a.heating = io->heating;
+    a.scratch = p->scratch.p;
+
+    const size_t smem = per_warp * warps;
+    CMB_CUDA(cudaFuncSetAttribute(flux_kernel<Real, FUSED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int64_t tasks = io->n_col * pt.parts;
+    const int64_t blocks = (tasks + warps - 1) / warps;
+    if (blocks > 0x7fffffffLL) {
+        set_error("too many columns for one launch");
+        return CMB200_ERR_LIMIT;
+    }
+    if (pt.n_slots || pt.parts == 1) {
+        flux_kernel<Real, FUSED><<<(unsigned)blocks, warps * 32, smem, s>>>(a);
+        CMB_LAUNCHED();
+    }
+    if (pt.parts > 1) {
+        flux_finalize_kernel<<<(unsigned)io->n_col, 128, L * sizeof(double), s>>>(
+            L, p->B, p->band_lo, p->band_hi, pt.n_slots, io->n_col, pt.band_slot0.p, p->band_delta.p,
+            p->scratch.p, p->P.p, a.g_over_cp, io->up, io->down, io->net, io->heating);
+        CMB_LAUNCHED();
+    }
+    return CMB200_OK;
+}
+
+static int validate_flux_io(const cmb200_plan *p, const cmb200_flux_io *io) {
+    CMB_CHECK_ARG(p && io, "null pointer");
+    CMB_CHECK_ARG(io->n_col >= 0, "negative column count");
+    if (io->n_col == 0) return CMB200_OK;
+    CMB_CHECK_ARG(io->T && io->T_g, "T and T_g are required");
+    if (io->tau) {
+        CMB_CHECK_ARG(io->n_tau >= 1, "n_tau must be >= 1 when tau is given");
+        CMB_CHECK_ARG(io->n_tau == 1 || io->tau_id, "tau_id is required when n_tau > 1");
+    } else {
+        if (p->M == 0) {
+            set_error("no tau given and the plan has no absorption tables (cmb200_plan_set_tables)");
+            return CMB200_ERR_STATE;
+        }
+        CMB_CHECK_ARG(io->q, "q is required for the table-fused path");
+    }
+    return CMB200_OK;
+}
+
+}  // namespace cmb
+
+using namespace cmb;
+
+extern "C" int cmb200_plan_set_tables(cmb200_plan *plan, int32_t M, const cmb200_table *tables) {
+    CMB_CHECK_ARG(plan && tables, "null pointer");
+    CMB_CHECK_ARG(M >= 1 && M <= kMaxMolecules, "between 1 and %d molecules supported, got %d", kMaxMolecules, M);
+    CMB_CUDA(cudaSetDevice(plan->device));
+    int nT_pad = 0;
+    for (int m = 0; m < M; ++m) {
+        int rc = check_table(&tables[m]);
+        if (rc) return rc;
+        nT_pad = std::max(nT_pad, (int)tables[m].n_T);
+    }
+    const int L = plan->L;
+    const int64_t N = plan->N, pitch = (N + 15) & ~(int64_t)15;
+    const size_t total = (size_t)M * L * nT_pad * pitch;
+    plan->KL64.release();
+    plan->KL32.release();
+    if (plan->precision == CMB200_F64)
+        CMB_CUDA(plan->KL64.alloc(total));
+    else
+        CMB_CUDA(plan->KL32.alloc(total));
+    std::vector<double> axes((size_t)M * nT_pad, 1e300);  // padding rows are never nearest
+    plan->nT.assign(M, 0);
+    DevBuf<double> dnu;
+    CMB_CUDA(dnu.upload(plan->hnu.data(), N));
+    for (int m = 0; m < M; ++m) {
+        const cmb200_table *t = &tables[m];
+        plan->nT[m] = t->n_T;
+        for (int i = 0; i < t->n_T; ++i) axes[(size_t)m * nT_pad + i] = t->T[i];
+        TableOnDevice dev;
+        int rc = dev.upload(t, 0);
+        if (rc) return rc;
+        DevBuf<int32_t> ip, inu;
+        CMB_CUDA(ip.alloc(L));
+        CMB_CUDA(inu.alloc(N));
+        if ((rc = launch_nearest(plan->P.p, L, dev.p.p, t->n_p, false, false, 0, 0, ip.p, 0))) return rc;
+        if ((rc = launch_nearest(dnu.p, N, dev.nu.p, t->n_nu, dev.nu_ascending, true, dev.nu_lo, dev.nu_hi, inu.p, 0)))
+            return rc;
+        dim3 grid((unsigned)((pitch + 255) / 256), (unsigned)L, (unsigned)nT_pad);
+        const size_t off = (size_t)m * L * nT_pad * pitch;
+        if (plan->precision == CMB200_F64)
+            level_table_kernel<double><<<grid, 256>>>(dev.k.p, t->n_T, t->n_nu, ip.p, inu.p, L, nT_pad, N, pitch, plan->KL64.p + off);
+        else
+            level_table_kernel<float><<<grid, 256>>>(dev.k.p, t->n_T, t->n_nu, ip.p, inu.p, L, nT_pad, N, pitch, plan->KL32.p + off);
+        CMB_LAUNCHED();
+        CMB_CUDA(cudaDeviceSynchronize());
+    }
+    CMB_CUDA(plan->T_axes.upload(axes.data(), axes.size()));
+    CMB_CUDA(cudaDeviceSynchronize());
+    plan->M = M;
+    plan->nT_pad = nT_pad;
+    plan->pitch = pitch;
+    plan->partition.n_col = -1;
+    return CMB200_OK;
+}
+
+extern "C" int cmb200_plan_optical_depth(cmb200_plan *plan, int64_t n_col, const double *T_tau,
+                                         const double *T_g, const double *q, int q_per_column,
+                                         double *tau, void *stream) {
+    CMB_CHECK_ARG(plan && q && tau, "null pointer");
+    CMB_CHECK_ARG(T_tau || T_g, "either T_tau or T_g is required");
+    CMB_CHECK_ARG(n_col >= 0, "negative column count");
+    if (plan->M == 0) {
+        set_error("the plan has no absorption tables (cmb200_plan_set_tables)");
+        return CMB200_ERR_STATE;
+    }
+    if (n_col == 0) return CMB200_OK;
+    CMB_CUDA(cudaSetDevice(plan->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    int rc = ensure_tidx(plan, n_col, T_tau, T_g, s);
+    if (rc) return rc;
+    dim3 grid((unsigned)((plan->N + 127) / 128), (unsigned)n_col);
+    CMB_CHECK_ARG(n_col <= 65535, "at most 65535 columns per optical-depth call");
+    if (plan->precision == CMB200_F64)
+        plan_optical_depth_kernel<double><<<grid, 128, 0, s>>>(plan->KL64.p, plan->M, plan->L, plan->nT_pad, plan->N,
+                                                              plan->pitch, plan->tidx.p, q, q_per_column ? plan->L : 0,
+                                                              n_col, plan->dx.p, plan->c.g, tau);
+    else
+        plan_optical_depth_kernel<float><<<grid, 128, 0, s>>>(plan->KL32.p, plan->M, plan->L, plan->nT_pad, plan->N,
+                                                             plan->pitch, plan->tidx.p, q, q_per_column ? plan->L : 0,
+                                                             n_col, plan->dx.p, plan->c.g, tau);
+    CMB_LAUNCHED();
+    return CMB200_OK;
+}
+
+extern "C" int cmb200_flux_workspace_bytes(cmb200_plan *plan, int64_t n_col, int64_t *bytes) {
+    CMB_CHECK_ARG(plan && bytes && n_col >= 0, "bad argument");
+    *bytes = (int64_t)n_col * plan->L * 8 + (int64_t)plan->M * n_col * plan->L;
+    return CMB200_OK;
+}
+
+extern "C" int cmb200_flux(cmb200_plan *plan, const cmb200_flux_io *io, void *stream) {
+    int rc = validate_flux_io(plan, io);
+    if (rc) return rc;
+    if (io->n_col == 0) return CMB200_OK;
+    CMB_CUDA(cudaSetDevice(plan->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    const int L = plan->L;
+    double *Tint = io->T_interface;
+    if (!Tint) {
+        size_t need = (size_t)io->n_col * L;
+        if (plan->Tint.n < need) CMB_CUDA(plan->Tint.alloc(need));
+        Tint = plan->Tint.p;
+    }
+    {
+        const int warps = 4;
+        interface_temperature_kernel<<<(unsigned)((io->n_col + warps - 1) / warps), warps * 32, 0, s>>>(
+            L, io->n_col, plan->splineT.p, io->T, io->T_g, Tint);
+        CMB_LAUNCHED();
+    }
+    const bool fused = io->tau == nullptr;
+    if (fused) {
+        rc = ensure_tidx(plan, io->n_col, io->T_tau, io->T_g, s);
+        if (rc) return rc;
+    }
+    if (plan->precision == CMB200_F64)
+        return fused ? launch_flux<double, true>(plan, io, Tint, s) : launch_flux<double, false>(plan, io, Tint, s);
+    return fused ? launch_flux<float, true>(plan, io, Tint, s) : launch_flux<float, false>(plan, io, Tint, s);
+}
+
+extern "C" int cmb200_flux_host(cmb200_plan *plan, const cmb200_flux_io *io) {
+    int rc = validate_flux_io(plan, io);
+    if (rc) return rc;
+    if (io->n_col == 0) return CMB200_OK;
+    CMB_CUDA(cudaSetDevice(plan->device));
+    const int64_t n = io->n_col;
+    const int L = plan->L, B = plan->B, M = plan->M;
+    cmb200_flux_io d = *io;
+    DevBuf<double> T, Tg, alb, tau, Ttau, q, up, down, net, heat, Tint;
+    DevBuf<int32_t> tid;
+    CMB_CUDA(T.upload(io->T, (size_t)n * (L - 1)));
+    d.T = T.p;
+    CMB_CUDA(Tg.upload(io->T_g, n));
+    d.T_g = Tg.p;
+    if (io->albedo) {
+        CMB_CUDA(alb.upload(io->albedo, n));
+        d.albedo = alb.p;
+    }
+    if (io->tau) {
+        CMB_CUDA(tau.upload(io->tau, (size_t)io->n_tau * L * plan->N));
+        d.tau = tau.p;
+        if (io->tau_id) {
+            for (int64_t i = 0; i < n; ++i)
+                CMB_CHECK_ARG(io->tau_id[i] >= 0 && io->tau_id[i] < io->n_tau, "tau_id[%lld] out of range", (long long)i);
+            CMB_CUDA(tid.upload(io->tau_id, n));
+            d.tau_id = tid.p;
+        }
+    } else {
+        if (io->T_tau) {
+            CMB_CUDA(Ttau.upload(io->T_tau, (size_t)n * L));
+            d.T_tau = Ttau.p;
+        }
+        CMB_CUDA(q.upload(io->q, (size_t)M * (io->q_per_column ? n : 1) * L));
+        d.q = q.p;
+    }
+    if (io->up) {
+        CMB_CUDA(up.alloc((size_t)n * L * B));
+        CMB_CUDA(cudaMemsetAsync(up.p, 0, up.n * sizeof(double)));
+        d.up = up.p;
+    }
+    if (io->down) {
+        CMB_CUDA(down.alloc((size_t)n * L * B));
+        CMB_CUDA(cudaMemsetAsync(down.p, 0, down.n * sizeof(double)));
+        d.down = down.p;
+    }
+    if (io->net) {
+        CMB_CUDA(net.alloc((size_t)n * L));
+        d.net = net.p;
+    }
+    if (io->heating) {
+        CMB_CUDA(heat.alloc((size_t)n * (L - 1)));
+        d.heating = heat.p;
+    }
+    if (io->T_interface) {
+        CMB_CUDA(Tint.alloc((size_t)n * L));
+        d.T_interface = Tint.p;
+    }
+    rc = cmb200_flux(plan, &d, nullptr);
+    if (rc) return rc;
+    if (io->up) CMB_CUDA(cudaMemcpyAsync(io->up, up.p, up.n * sizeof(double), cudaMemcpyDeviceToHost));
+    if (io->down) CMB_CUDA(cudaMemcpyAsync(io->down, down.p, down.n * sizeof(double), cudaMemcpyDeviceToHost));
+    if (io->net) CMB_CUDA(cudaMemcpyAsync(io->net, net.p, net.n * sizeof(double), cudaMemcpyDeviceToHost));
+    if (io->heating) CMB_CUDA(cudaMemcpyAsync(io->heating, heat.p, heat.n * sizeof(double), cudaMemcpyDeviceToHost));
+    if (io->T_interface) CMB_CUDA(cudaMemcpyAsync(io->T_interface, Tint.p, Tint.n * sizeof(double), cudaMemcpyDeviceToHost));
+    CMB_CUDA(cudaDeviceSynchronize());
+    return CMB200_OK;
+}

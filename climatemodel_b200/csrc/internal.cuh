@@ -1,0 +1,68 @@
+// Library-internal declarations: the plan object and the launchers shared between .cu files.
+#pragma once
+#include <vector>
+
+#include "common.cuh"
+
+namespace cmb {
+
+constexpr int kMaxMolecules = 8;
+constexpr int kChains = 1;  // wavenumber bins per lane and pass of the flux kernel (R)
+
+int check_table(const cmb200_table *t);
+int launch_nearest(const double *d_values, int64_t n, const double *d_axis, int n_axis,
+                   bool axis_ascending, bool crop, double lo, double hi, int32_t *d_out,
+                   cudaStream_t s);
+
+// Work decomposition of one flux evaluation, cached per (n_col) on the plan.
+struct Partition {
+    int64_t n_col = -1;
+    int parts = 0;       // warps per column
+    int n_slots = 0;     // partial-sum slots per column (parts > 1 only)
+    DevBuf<int32_t> part_seg0, part_slot0, band_slot0;
+};
+
+}  // namespace cmb
+
+struct cmb200_plan {
+    int device = 0;
+    int precision = CMB200_F64;
+    cmb200_constants c{};
+    int L = 0, B = 0;
+    int64_t N = 0;
+    // host copies
+    std::vector<double> hP, hnu, hcentre, hdelta;
+    std::vector<int32_t> hstart, hlen;
+    std::vector<uint8_t> hsw;
+    int band_lo = 0, band_hi = 0;
+    // star (real_gas.py:246)
+    double T_star = 5778.0, R_star = 6.96340e8, dist = 1.495978707e11;
+    // device: grid
+    cmb::DevBuf<double> P, dx, hdP, geo, splineT;
+    // device: bands and chains
+    cmb::DevBuf<int32_t> band_start, band_len;
+    cmb::DevBuf<double> band_centre, band_delta, band_sumw, wchain64;
+    cmb::DevBuf<float> wchain32;
+    cmb::DevBuf<uint8_t> band_sw;
+    cmb::DevBuf<int64_t> chain_off;
+    int64_t n_chains = 0;
+    // device: segments (runs of 32*kChains bins inside one band) for bands [band_lo, band_hi)
+    cmb::DevBuf<int32_t> seg_band, seg_c0;
+    std::vector<int32_t> hseg_band;
+    int n_seg = 0;
+    // device: level table KL[M][L][nT_pad][pitch]
+    int M = 0, nT_pad = 0;
+    int64_t pitch = 0;
+    std::vector<int> nT;
+    cmb::DevBuf<double> KL64, T_axes;  // T_axes[M][nT_pad]
+    cmb::DevBuf<float> KL32;
+    cmb::Partition partition;
+    // per-call scratch kept between calls (grown on demand)
+    cmb::DevBuf<double> Tint, scratch;
+    cmb::DevBuf<uint8_t> tidx;
+};
+
+namespace cmb {
+int build_segments(cmb200_plan *p);
+int spline_operator_host(const double *P, int L, std::vector<double> &At);
+}  // namespace cmb

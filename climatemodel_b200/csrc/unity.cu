@@ -1,0 +1,7 @@
+// Single translation unit of libclimatemodel_b200.so: the kernels are launched across what
+// would otherwise be file boundaries, and one TU avoids relocatable device code.
+#include "plan.cu"
+#include "tables.cu"
+#include "flux.cu"
+#include "transmission.cu"
+#include "peaks.cu"
