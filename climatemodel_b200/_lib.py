@@ -72,6 +72,8 @@ SIGNATURES = {
     'cmb200_plan_set_star': (C.c_int, [C.c_void_p, C.c_double, C.c_double, C.c_double]),
     'cmb200_plan_set_tables': (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(Table)]),
     'cmb200_plan_set_band_range': (C.c_int, [C.c_void_p, C.c_int32, C.c_int32]),
+    'cmb200_plan_segments': (C.c_int, [C.c_void_p, c_int32_p, C.POINTER(C.c_int64)]),
+    'cmb200_plan_set_segment_range': (C.c_int, [C.c_void_p, C.c_int64, C.c_int64]),
     'cmb200_plan_info': (C.c_int, [C.c_void_p, c_int32_p, C.POINTER(C.c_int64), c_int32_p, c_int32_p,
                                    c_int32_p, c_int32_p, C.POINTER(C.c_int64)]),
     'cmb200_plan_optical_depth': (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,

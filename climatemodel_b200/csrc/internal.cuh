@@ -35,6 +35,7 @@ struct cmb200_plan {
     std::vector<int32_t> hstart, hlen;
     std::vector<uint8_t> hsw;
     int band_lo = 0, band_hi = 0;
+    int64_t seg_lo = 0, seg_hi = (int64_t)1 << 62, n_seg_total = 0;
     // star (real_gas.py:246)
     double T_star = 5778.0, R_star = 6.96340e8, dist = 1.495978707e11;
     // device: grid

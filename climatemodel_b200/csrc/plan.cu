@@ -144,11 +144,14 @@ static void pressure_quadrature(const std::vector<double> &P, std::vector<double
 int build_segments(cmb200_plan *p) {
     std::vector<int32_t> sb, sc;
     const int span = 32 * kChains;
-    for (int j = p->band_lo; j < p->band_hi; ++j)
-        for (int c0 = 0; c0 < p->hlen[j]; c0 += span) {
+    int64_t g = 0;  // segment index over the whole band list
+    for (int j = 0; j < p->B; ++j)
+        for (int c0 = 0; c0 < p->hlen[j]; c0 += span, ++g) {
+            if (j < p->band_lo || j >= p->band_hi || g < p->seg_lo || g >= p->seg_hi) continue;
             sb.push_back(j);
             sc.push_back(c0);
         }
+    p->n_seg_total = g;
     p->n_seg = (int)sb.size();
     p->hseg_band = sb;
     CMB_CUDA(p->seg_band.upload(sb.data(), sb.size()));
@@ -296,6 +299,22 @@ extern "C" int cmb200_plan_set_band_range(cmb200_plan *plan, int32_t band_lo, in
     plan->band_lo = band_lo;
     plan->band_hi = band_hi;
     return build_segments(plan);
+}
+
+extern "C" int cmb200_plan_set_segment_range(cmb200_plan *plan, int64_t seg_lo, int64_t seg_hi) {
+    CMB_CHECK_ARG(plan, "null plan");
+    CMB_CHECK_ARG(0 <= seg_lo && seg_lo <= seg_hi, "bad segment range");
+    CMB_CUDA(cudaSetDevice(plan->device));
+    plan->seg_lo = seg_lo;
+    plan->seg_hi = seg_hi;
+    return build_segments(plan);
+}
+
+extern "C" int cmb200_plan_segments(const cmb200_plan *plan, int32_t *bins_per_segment, int64_t *n_segments) {
+    CMB_CHECK_ARG(plan, "null plan");
+    if (bins_per_segment) *bins_per_segment = 32 * kChains;
+    if (n_segments) *n_segments = plan->n_seg_total;
+    return CMB200_OK;
 }
 
 extern "C" int cmb200_plan_info(const cmb200_plan *plan, int32_t *L, int64_t *N, int32_t *B,

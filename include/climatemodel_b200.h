@@ -118,6 +118,12 @@ int cmb200_plan_set_tables(cmb200_plan *plan, int32_t M, const cmb200_table *tab
 /* Restrict the plan to bands [band_lo, band_hi): wavenumber-band sharding across GPUs
  * (SURVEY.md 8e).  Outputs net/heating then hold this shard's partial band sums. */
 int cmb200_plan_set_band_range(cmb200_plan *plan, int32_t band_lo, int32_t band_hi);
+/* Finer shard unit: a segment is a run of bins_per_segment consecutive bins inside one band
+ * (bands are enumerated in order, each split into ceil(len/bins_per_segment) segments).
+ * Restricting a plan to segments [seg_lo, seg_hi) lets ranks balance work when one band holds
+ * a large share of the bins; up/down/net are then partial sums to be added across ranks. */
+int cmb200_plan_segments(const cmb200_plan *plan, int32_t *bins_per_segment, int64_t *n_segments);
+int cmb200_plan_set_segment_range(cmb200_plan *plan, int64_t seg_lo, int64_t seg_hi);
 int cmb200_plan_info(const cmb200_plan *plan, int32_t *L, int64_t *N, int32_t *B, int32_t *M,
                      int32_t *nT, int32_t *precision, int64_t *n_chains);
 

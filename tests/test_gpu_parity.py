@@ -1,0 +1,297 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (ctypes), against the golden
+vectors produced by the unmodified reference and against the CPU oracle on seeded inputs.
+
+Tolerances (BASELINE.json north_star): FP64 mode max|d|/max|ref| <= 1e-10 on fluxes, net flux
+and heating rate; FP32 mode <= 1e-5.  Integer / gather work and optical depth: bit-exact.
+"""
+import os
+
+import numpy as np
+import pytest
+
+import oracle.realgas_oracle as orc
+from util import CASES, GOLDEN, load_case, load_table, relmax
+
+pytestmark = pytest.mark.gpu
+
+TOL64 = 1e-10
+TOL32 = 1e-5
+
+
+@pytest.fixture(scope='module')
+def rg():
+    import climatemodel_b200.radiation.real_gas as m
+    return m
+
+
+def make_plan(c, precision='f64', tables=False):
+    from climatemodel_b200.plan import FluxPlan
+    return FluxPlan(c['P'], c['nu'], c['bands'], tables=c['tables'] if tables else None, precision=precision,
+                    T_star=c['T_star'], R_star=c['R_star'], star_planet_dist=c['dist'])
+
+
+def oracle_tau(c):
+    return orc.optical_depth(c['P'], c['T_interface_tau'], c['nu'], c['tables'], list(c['q']))
+
+
+# ---- A1 / A2 ---------------------------------------------------------------------------------
+def test_planck_and_gather_vectors(rg):
+    f = np.load(os.path.join(GOLDEN, 'functions.npz'))
+    B = rg.B_wavenumber(f['planck_nu'], f['planck_T'])
+    assert B.shape == f['planck_B'].shape
+    np.testing.assert_allclose(B, f['planck_B'], rtol=2e-13, atol=0)
+    tab = load_table('CO2_no_sw')
+    k = rg.get_absorption_coef(f['gather_p'], f['gather_T'], f['gather_nu'], tab)
+    assert np.array_equal(k, f['gather_k'])
+    from climatemodel_b200.radiation import real_gas as m
+    k2 = m._gather(f['gather_p'], f['gather_T'], f['load_nu'], tab, zero_outside=True)
+    assert np.array_equal(k2, f['load_k'])
+
+
+def test_gather_long_axis_bisection_matches_linear_scan(rg):
+    rng = np.random.default_rng(1)
+    tab = {'p': np.array([1e5, 1e4, 1e3]), 'T': np.array([250., 300.]),
+           'nu': np.arange(0, 3000, 2.5), 'absorption_coef': rng.random((3, 2, 1200))}
+    nu = np.concatenate((rng.uniform(-10, 3010, 500), tab['nu'][:50] + 1.25, tab['nu'][:50]))
+    p = np.array([2e5, 3e4, 5.5e3, 10.])
+    T = np.array([100., 275., 275.1, 400.])
+    k = rg.get_absorption_coef(p, T, nu, tab)
+    assert np.array_equal(k, orc.gather_absorption_coef(p, T, nu, tab))
+
+
+# ---- A3 ------------------------------------------------------------------------------------
+@pytest.mark.parametrize('name', CASES)
+def test_optical_depth_bit_exact(rg, name):
+    c = load_case(name)
+    tau = rg.optical_depth_from_tables(c['P'], c['T_interface_tau'], c['nu'], c['tables'], c['q'])
+    assert np.array_equal(tau[:, c['tau_sub_idx']], c['tau_sub'])
+    assert np.array_equal(tau, oracle_tau(c))
+
+
+def test_optical_depth_empty_and_unsorted(rg):
+    c = load_case('single_line_nz30')
+    tau = rg.optical_depth_from_tables(c['P'], c['T_interface_tau'], c['nu'][:0], c['tables'], c['q'])
+    assert tau.shape == (30, 0)
+    with pytest.raises(ValueError):
+        rg.optical_depth_from_tables(c['P'][::-1], c['T_interface_tau'], c['nu'], c['tables'], c['q'])
+
+
+# ---- A4 / A5 ---------------------------------------------------------------------------------
+@pytest.mark.parametrize('name', ['co2_nz50_earth', 'two_mol_nz41'])
+def test_transmission_matrix(rg, name):
+    c = load_case(name)
+    tau = oracle_tau(c)
+    j = int(c['trans_band'])
+    s, n = int(c['band_start'][j]), int(c['band_len'][j])
+    Tr = rg.transmission(c['P'], c['P'], c['P'], c['nu'][s:s + n], c['band_delta'][j], c['nu'], tau)
+    low = np.tril_indices(c['P'].size, -1)
+    ref_full = orc.transmission(c['P'], c['P'], c['P'], c['nu'][s:s + n], c['band_delta'][j], c['nu'], tau)
+    # lower triangle: overflowing entries overflow on both sides
+    assert np.array_equal(np.isinf(Tr[low]), np.isinf(ref_full[low]))
+    Tr = np.triu(np.nan_to_num(Tr, nan=0.0, posinf=0.0))
+    assert relmax(Tr, c['trans_upper']) < 1e-13
+
+
+def test_transmission_subset_and_errors(rg):
+    c = load_case('co2_nz50_earth')
+    tau = oracle_tau(c)
+    j = 3
+    s, n = int(c['band_start'][j]), int(c['band_len'][j])
+    a = rg.transmission(c['P'][5:9], c['P'][-1:], c['P'], c['nu'][s:s + n], c['band_delta'][j], c['nu'], tau)
+    b = orc.transmission(c['P'][5:9], c['P'][-1:], c['P'], c['nu'][s:s + n], c['band_delta'][j], c['nu'], tau)
+    assert a.shape == (4, 1) and relmax(a, b) < 1e-13
+    with pytest.raises(ValueError):
+        rg.transmission(np.array([1.2345]), c['P'], c['P'], c['nu'][:4], 30.0, c['nu'], tau)
+
+
+def test_dtransmission_dq(rg):
+    c = load_case('two_mol_nz41')
+    tau = oracle_tau(c)
+    j = int(c['dtdq_band'])
+    a, b = c['dtdq_rows']
+    s, n = int(c['band_start'][j]), int(c['band_len'][j])
+    d = rg.dtransmission_dq(c['P'][a:a + 1], c['P'][b:b + 1], c['P'], c['nu'][s:s + n], c['band_delta'][j],
+                            c['nu'], tau, c['dtdq_k'])
+    assert relmax(d, c['dtdq']) < 1e-13
+
+
+# ---- A6-A9: resident tau ----------------------------------------------------------------------
+def check_flux(out, c, tol, heating_tol=None):
+    assert relmax(out['up'][0], c['up']) < tol
+    assert relmax(out['down'][0], c['down']) < tol
+    assert relmax(out['net'][0], c['net']) < tol
+    assert relmax(out['heating'][0], c['heating']) < (heating_tol or tol)
+
+
+@pytest.mark.parametrize('name', CASES)
+def test_flux_from_tau_fp64(name):
+    c = load_case(name)
+    plan = make_plan(c)
+    out = plan.flux(c['T'], c['T_g'], tau=oracle_tau(c), albedo=c['albedo'],
+                    outputs=('up', 'down', 'net', 'heating', 'T_interface'))
+    assert np.abs(out['T_interface'][0] - c['T_interface']).max() < 1e-9
+    check_flux(out, c, TOL64)
+
+
+@pytest.mark.parametrize('name', CASES)
+def test_flux_fused_from_tables_fp64(name):
+    c = load_case(name)
+    plan = make_plan(c, tables=True)
+    out = plan.flux(c['T'], c['T_g'], T_tau=c['T_interface_tau'], q=c['q'], albedo=c['albedo'])
+    check_flux(out, c, TOL64)
+
+
+@pytest.mark.parametrize('name', CASES)
+def test_flux_fp32_mode(name):
+    c = load_case(name)
+    plan = make_plan(c, precision='f32', tables=True)
+    out = plan.flux(c['T'], c['T_g'], tau=oracle_tau(c), albedo=c['albedo'])
+    assert relmax(out['up'][0], c['up']) < TOL32
+    assert relmax(out['down'][0], c['down']) < TOL32
+    assert relmax(out['net'][0], c['net']) < TOL32
+    out = plan.flux(c['T'], c['T_g'], T_tau=c['T_interface_tau'], q=c['q'], albedo=c['albedo'])
+    assert relmax(out['up'][0], c['up']) < TOL32
+    assert relmax(out['down'][0], c['down']) < TOL32
+    assert relmax(out['net'][0], c['net']) < TOL32
+
+
+# ---- batched columns ------------------------------------------------------------------------------
+def batch_inputs(c, n_col, seed=0):
+    rng = np.random.default_rng(seed)
+    L = c['P'].size
+    T = c['T'][None, :] + rng.normal(0, 3.0, (n_col, L - 1))
+    T_g = c['T_g'] + rng.normal(0, 3.0, n_col)
+    T_tau = c['T_interface_tau'][None, :] + rng.uniform(-25, 25, (n_col, L))
+    albedo = rng.uniform(0.1, 0.5, n_col)
+    q = c['q'][:, None, :] * rng.uniform(0.5, 2.0, (c['q'].shape[0], n_col, 1))
+    return T, T_g, T_tau, albedo, np.ascontiguousarray(q)
+
+
+def oracle_column(c, T, T_g, T_tau, albedo, q):
+    I = orc.layer_integrand(c['P'], T_tau, c['nu'], c['tables'], list(q))
+    up, dn = orc.get_flux_per_bin(c['P'], T, T_g, I, c['nu'], c['bands'], c['T_star'], c['R_star'], c['dist'], albedo)
+    net = orc.net_flux(up, dn, c['band_delta'])
+    return up, dn, net, orc.heating_rate(net, c['P'])
+
+
+@pytest.mark.parametrize('name,n_col', [('two_mol_nz41', 37), ('co2_nz50_earth', 5)])
+def test_batched_fused_columns_against_oracle(name, n_col):
+    c = load_case(name)
+    plan = make_plan(c, tables=True)
+    T, T_g, T_tau, albedo, q = batch_inputs(c, n_col)
+    out = plan.flux(T, T_g, T_tau=T_tau, q=q, albedo=albedo)
+    for i in range(n_col):
+        up, dn, net, heat = oracle_column(c, T[i], T_g[i], T_tau[i], albedo[i], q[:, i])
+        assert relmax(out['up'][i], up) < TOL64
+        assert relmax(out['down'][i], dn) < TOL64
+        assert relmax(out['net'][i], net) < TOL64
+        assert relmax(out['heating'][i], heat) < TOL64
+
+
+def test_whole_column_mode_equals_split_mode():
+    """Few columns are split over many warps (partial sums + finalize kernel); many columns run
+    one warp per column with the epilogue fused.  Same column, both ways."""
+    c = load_case('two_mol_nz41')
+    plan = make_plan(c, tables=True)
+    T, T_g, T_tau, albedo, q = batch_inputs(c, 3, seed=5)
+    few = plan.flux(T, T_g, T_tau=T_tau, q=q, albedo=albedo)
+    n_rep = 1200                                     # > 148 SMs x warps x 2 -> whole-column mode
+    rep = lambda a: np.ascontiguousarray(np.tile(a, (n_rep,) + (1,) * (a.ndim - 1)))
+    many = plan.flux(rep(T), rep(T_g), T_tau=rep(T_tau), albedo=rep(albedo),
+                     q=np.ascontiguousarray(np.tile(q, (1, n_rep, 1))))
+    for k in ('up', 'down', 'net', 'heating'):
+        assert relmax(many[k][:3], few[k]) < 1e-13
+        assert np.array_equal(many[k][:3], many[k][-3:])         # deterministic across warps
+
+
+def test_tau_id_selects_table():
+    c = load_case('co2_nz50_earth')
+    plan = make_plan(c)
+    tau = oracle_tau(c)
+    taus = np.stack([tau, 0.5 * tau, 2.0 * tau])
+    ids = np.array([2, 0, 1, 0], dtype=np.int32)
+    T = np.tile(c['T'], (4, 1))
+    out = plan.flux(T, np.full(4, c['T_g']), tau=taus, tau_id=ids, albedo=c['albedo'])
+    for i, t in enumerate(ids):
+        one = plan.flux(c['T'], c['T_g'], tau=taus[t], albedo=c['albedo'])
+        assert relmax(out['net'][i], one['net'][0]) < 1e-13
+    assert relmax(out['up'][1], c['up']) < TOL64
+
+
+def test_band_sharding_partial_nets_add_up():
+    c = load_case('two_mol_nz41')
+    full = make_plan(c, tables=True).flux(c['T'], c['T_g'], T_tau=c['T_interface_tau'], q=c['q'], albedo=c['albedo'])
+    B = len(c['band_centre'])
+    cuts = [0, B // 3, B // 2, B]
+    net = np.zeros_like(full['net'])
+    up = np.zeros_like(full['up'])
+    for lo, hi in zip(cuts[:-1], cuts[1:]):
+        plan = make_plan(c, tables=True)
+        plan.set_band_range(lo, hi)
+        part = plan.flux(c['T'], c['T_g'], T_tau=c['T_interface_tau'], q=c['q'], albedo=c['albedo'])
+        net += part['net']
+        up += part['up']
+        assert np.all(part['up'][:, :, :lo] == 0) and np.all(part['up'][:, :, hi:] == 0)
+    assert relmax(net, full['net']) < 1e-13
+    assert relmax(up, full['up']) < 1e-13
+
+
+# ---- size-independent properties at a larger size ----------------------------------------------------
+def test_properties_larger_grid():
+    """10k-bin synthetic table, 100 levels, 64 columns: (i) zero absorber => up flux is the
+    surface emission at every level and the down flux the TOA value; (ii) fluxes are linear in
+    the star term: doubling (1 - albedo) doubles down-flux of the short-wave bands;
+    (iii) two random columns agree with the oracle at this size."""
+    rng = np.random.default_rng(3)
+    L, N, B = 100, 10401, 40
+    P = np.sort(10 ** (np.log10(101320.) + 1 - 10 ** (np.log10(np.log10(101320.) - np.log10(20.) + 1) / (L - 1) * np.arange(L))))
+    nu = np.arange(N) * 5.0
+    edges = np.linspace(0, N - 1, B + 1).astype(int)
+    bands = {'start': edges[:-1].astype(np.int32), 'len': (np.diff(edges) + 1).astype(np.int32),
+             'centre': nu[(edges[:-1] + edges[1:]) // 2], 'delta': nu[edges[1:]] - nu[edges[:-1]],
+             'sw': (nu[edges[:-1]] > 3000).astype(np.uint8)}
+    tab = {'p': np.logspace(5.1, 1, 30), 'T': np.array([200., 250., 300.]), 'nu': nu,
+           'absorption_coef': 10 ** rng.uniform(-6, 2, (30, 3, N))}
+    from climatemodel_b200.plan import FluxPlan
+    plan = FluxPlan(P, nu, bands, tables=[tab])
+    n_col = 64
+    T = np.full((n_col, L - 1), 260.0)
+    T_g = np.full(n_col, 260.0)
+    # (i)
+    out = plan.flux(T, T_g, q=np.zeros((1, L)), albedo=0.3, outputs=('up', 'down'))
+    assert np.abs(out['up'] - out['up'][:, -1:, :]).max() <= 1e-12 * np.abs(out['up']).max()
+    assert np.abs(out['down'] - out['down'][:, :1, :]).max() <= 1e-12 * np.abs(out['down']).max()
+    # (ii)
+    q = np.full((1, L), 1e-3)
+    a = plan.flux(T, T_g, q=q, albedo=0.4, outputs=('down',))['down']
+    b = plan.flux(T, T_g, q=q, albedo=0.7, outputs=('down',))['down']
+    sw = bands['sw'].astype(bool)
+    assert relmax(a[:, :, sw], 2.0 * b[:, :, sw]) < 1e-13
+    # (iii) two perturbed columns at this size against the oracle's per-bin form
+    T2 = 260.0 + rng.normal(0, 5, (2, L - 1))
+    Tg2 = np.array([262.0, 255.0])
+    Ttau = 250.0 + rng.uniform(-60, 60, (2, L))
+    q2 = 10 ** rng.uniform(-5, -2, (1, 2, L))
+    out = plan.flux(T2, Tg2, T_tau=Ttau, q=q2, albedo=0.3)
+    c = {'P': P, 'nu': nu, 'tables': [tab], 'bands': bands, 'T_star': 5778., 'R_star': 6.96340e8,
+         'dist': 1.495978707e11, 'band_delta': bands['delta']}
+    for i in range(2):
+        up, dn, net, heat = oracle_column(c, T2[i], Tg2[i], Ttau[i], 0.3, q2[:, i])
+        assert relmax(out['up'][i], up) < TOL64
+        assert relmax(out['down'][i], dn) < TOL64
+        assert relmax(out['net'][i], net) < TOL64
+        assert relmax(out['heating'][i], heat) < TOL64
+
+
+def test_errors():
+    c = load_case('single_line_nz30')
+    plan = make_plan(c)
+    with pytest.raises(ValueError):
+        plan.flux(c['T'][:-1], c['T_g'], tau=oracle_tau(c))
+    with pytest.raises(Exception):
+        plan.flux(c['T'], c['T_g'], q=c['q'])         # no tables on the plan
+    from climatemodel_b200.plan import FluxPlan
+    with pytest.raises(ValueError):
+        FluxPlan(c['P'][::-1], c['nu'], c['bands'])
+    with pytest.raises(ValueError):
+        FluxPlan(c['P'][:4], c['nu'], c['bands'])
