@@ -62,10 +62,11 @@ static int ensure_partition(cmb200_plan *p, int64_t n_col, int warps_per_cta) {
     return CMB200_OK;
 }
 
-template <typename Real, bool FUSED>
+template <typename Real, int MM>
 static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *Tint, cudaStream_t s) {
     const int L = p->L;
-    const size_t per_warp = flux_warp_smem<Real, FUSED>(L, p->M);
+    constexpr bool FUSED = MM > 0;
+    const size_t per_warp = flux_warp_smem<Real, FUSED>(L, MM);
     int max_smem = 0;
     CMB_CUDA(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, p->device));
     int warps = (int)std::min<size_t>(8, (size_t)max_smem / per_warp);
@@ -130,7 +131,7 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     a.scratch = p->scratch.p;
 
     const size_t smem = per_warp * warps;
-    CMB_CUDA(cudaFuncSetAttribute(flux_kernel<Real, FUSED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CMB_CUDA(cudaFuncSetAttribute(flux_kernel<Real, MM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int64_t tasks = io->n_col * pt.parts;
     const int64_t blocks = (tasks + warps - 1) / warps;
     if (blocks > 0x7fffffffLL) {
@@ -138,7 +139,7 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
         return CMB200_ERR_LIMIT;
     }
     if (pt.n_slots || pt.parts == 1) {
-        flux_kernel<Real, FUSED><<<(unsigned)blocks, warps * 32, smem, s>>>(a);
+        flux_kernel<Real, MM><<<(unsigned)blocks, warps * 32, smem, s>>>(a);
         CMB_LAUNCHED();
     }
     if (pt.parts > 1) {
@@ -148,6 +149,11 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
         CMB_LAUNCHED();
     }
     return CMB200_OK;
+}
+
+__global__ void exp_neg_test_kernel(const double *__restrict__ x, int64_t n, double *__restrict__ out) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i < n) out[i] = exp_neg(x[i]);
 }
 
 static int validate_flux_io(const cmb200_plan *p, const cmb200_flux_io *io) {
@@ -285,9 +291,26 @@ extern "C" int cmb200_flux(cmb200_plan *plan, const cmb200_flux_io *io, void *st
         rc = ensure_tidx(plan, io->n_col, io->T_tau, io->T_g, s);
         if (rc) return rc;
     }
-    if (plan->precision == CMB200_F64)
-        return fused ? launch_flux<double, true>(plan, io, Tint, s) : launch_flux<double, false>(plan, io, Tint, s);
-    return fused ? launch_flux<float, true>(plan, io, Tint, s) : launch_flux<float, false>(plan, io, Tint, s);
+    const int mm = fused ? plan->M : 0;
+    if (plan->precision == CMB200_F64) {
+        switch (mm) {
+            case 0: return launch_flux<double, 0>(plan, io, Tint, s);
+            case 1: return launch_flux<double, 1>(plan, io, Tint, s);
+            case 2: return launch_flux<double, 2>(plan, io, Tint, s);
+            case 3: return launch_flux<double, 3>(plan, io, Tint, s);
+            case 4: return launch_flux<double, 4>(plan, io, Tint, s);
+        }
+    } else {
+        switch (mm) {
+            case 0: return launch_flux<float, 0>(plan, io, Tint, s);
+            case 1: return launch_flux<float, 1>(plan, io, Tint, s);
+            case 2: return launch_flux<float, 2>(plan, io, Tint, s);
+            case 3: return launch_flux<float, 3>(plan, io, Tint, s);
+            case 4: return launch_flux<float, 4>(plan, io, Tint, s);
+        }
+    }
+    set_error("unsupported molecule count %d", mm);
+    return CMB200_ERR_LIMIT;
 }
 
 extern "C" int cmb200_flux_host(cmb200_plan *plan, const cmb200_flux_io *io) {
@@ -355,5 +378,17 @@ extern "C" int cmb200_flux_host(cmb200_plan *plan, const cmb200_flux_io *io) {
     if (io->heating) CMB_CUDA(cudaMemcpyAsync(io->heating, heat.p, heat.n * sizeof(double), cudaMemcpyDeviceToHost));
     if (io->T_interface) CMB_CUDA(cudaMemcpyAsync(io->T_interface, Tint.p, Tint.n * sizeof(double), cudaMemcpyDeviceToHost));
     CMB_CUDA(cudaDeviceSynchronize());
+    return CMB200_OK;
+}
+
+extern "C" int cmb200_test_exp_neg_host(const double *x, int64_t n, double *out) {
+    CMB_CHECK_ARG(x && out && n >= 0, "bad argument");
+    if (n == 0) return CMB200_OK;
+    DevBuf<double> dx, dout;
+    CMB_CUDA(dx.upload(x, n));
+    CMB_CUDA(dout.alloc(n));
+    exp_neg_test_kernel<<<(unsigned)((n + 255) / 256), 256>>>(dx.p, n, dout.p);
+    CMB_LAUNCHED();
+    CMB_CUDA(cudaMemcpy(out, dout.p, n * sizeof(double), cudaMemcpyDeviceToHost));
     return CMB200_OK;
 }

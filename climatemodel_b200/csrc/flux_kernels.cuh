@@ -8,10 +8,10 @@
 // is one exp per layer plus two first-order recurrences over the layers, and the band value is
 // the trapezoid-weighted sum of the chains.
 //
-// Mapping: one warp owns one (column, part) task; lanes hold kChains chains each
+// Mapping: one warp owns one (column, part) task; each lane holds one chain at a time
 // (consecutive lanes = consecutive wavenumber bins, so table / tau rows are read coalesced).
 // The downward sweep (TOA -> surface) computes t_k and parks it in shared memory
-// ts[k][chain][lane]; the upward sweep (surface -> TOA) replays it, so each layer costs one
+// ts[k][lane]; the upward sweep (surface -> TOA) replays it, so each layer costs one
 // exp, not two.  Per interface the chains are summed over the warp with shuffles and added to
 // the band accumulators; bands are folded into net flux and heating rate in the epilogue.
 #pragma once
@@ -70,16 +70,72 @@ __host__ __device__ inline size_t flux_warp_smem(int L, int M) {
     return WarpSmem<Real, FUSED>(L, M).total;
 }
 
-__device__ __forceinline__ double exp_neg(double x) { return exp(-x); }
+constexpr int kU = 8;   // layers per block of the sweeps (instruction-level parallelism)
+
+// exp(-x) for the layer transmissivity.  FP64: n = rint(-x log2 e), r = -x - n ln2 (two-term
+// Cody-Waite), degree-11 near-minimax polynomial on |r| <= ln2/2 (max rel. error 1.6e-17 before
+// rounding), scaled by 2^n through the exponent field.  Arguments beyond exp(-708) clamp there
+// (3e-308, nothing at the 1e-10 parity level); no other special cases are needed on this path.
+__device__ __forceinline__ double exp_neg(double x) {
+    double y = fmin(fmax(-x, -708.0), 709.0);
+    const double shifter = 6755399441055744.0;                 // 1.5 * 2^52
+    double tn = fma(y, 1.4426950408889634074, shifter);
+    const int n = __double2loint(tn);
+    tn -= shifter;
+    double r = fma(tn, -6.93147180369123816490e-01, y);
+    r = fma(tn, -1.90821492927058770002e-10, r);
+    double p = 2.51100492048186583e-08;
+    p = fma(p, r, 2.76326547225277896e-07);
+    p = fma(p, r, 2.75572408872298695e-06);
+    p = fma(p, r, 2.48014854415613131e-05);
+    p = fma(p, r, 1.98412698900764028e-04);
+    p = fma(p, r, 1.38888889523528631e-03);
+    p = fma(p, r, 8.33333333331958900e-03);
+    p = fma(p, r, 4.16666666664879531e-02);
+    p = fma(p, r, 1.66666666666666796e-01);
+    p = fma(p, r, 5.00000000000001887e-01);
+    p = fma(p, r, 1.0);
+    p = fma(p, r, 1.0);
+    return __hiloint2double(__double2hiint(p) + (n << 20), __double2loint(p));
+}
 __device__ __forceinline__ float exp_neg(float x) { return __expf(-x); }
 
-template <typename Real, bool FUSED>
+// Sum eight per-lane values over the warp at once: three exchange steps that halve the number
+// of values a lane carries while doubling the lanes each partial sum covers, then two plain
+// butterfly steps -- 9 additions and 9 shuffles for 8 sums instead of 40 + 40.  Afterwards
+// every lane holds the total of value ((lane>>4)&1)*4 + ((lane>>3)&1)*2 + ((lane>>2)&1).
+template <typename Real>
+__device__ __forceinline__ Real reduce8(const Real (&v)[8], int lane) {
+    const unsigned full = 0xffffffffu;
+    const bool h4 = lane & 16, h3 = lane & 8, h2 = lane & 4;
+    Real a4[4], a2[2];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const Real keep = h4 ? v[i + 4] : v[i], send = h4 ? v[i] : v[i + 4];
+        a4[i] = keep + __shfl_xor_sync(full, send, 16);
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const Real keep = h3 ? a4[i + 2] : a4[i], send = h3 ? a4[i] : a4[i + 2];
+        a2[i] = keep + __shfl_xor_sync(full, send, 8);
+    }
+    const Real keep = h2 ? a2[1] : a2[0], send = h2 ? a2[0] : a2[1];
+    Real c = keep + __shfl_xor_sync(full, send, 4);
+    c += __shfl_xor_sync(full, c, 2);
+    c += __shfl_xor_sync(full, c, 1);
+    return c;
+}
+
+// MM = number of molecules of the table-fused path (compile-time so the prefetched table values
+// live in registers); MM = 0 selects the resident-tau path.
+template <typename Real, int MM>
 __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    constexpr int R = kChains;
+    constexpr bool FUSED = MM > 0;
+    constexpr int MR = MM > 0 ? MM : 1;
     using Src = typename std::conditional<FUSED, Real, double>::type;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int L = a.L, nl = a.L - 1, M = a.M;
+    const int L = a.L, nl = a.L - 1, M = MM;
     const int64_t task = (int64_t)blockIdx.x * (blockDim.x >> 5) + warp;
     if (task >= a.n_col * a.parts) return;
     const int64_t col = task / a.parts;
@@ -176,101 +232,110 @@ __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
                 __syncwarp();
             }
         }
-        // ---- this segment's chains -----------------------------------------------------------
-        const int len = a.band_len[j];
-        Real w[R];
-        int64_t n[R];
-#pragma unroll
-        for (int r = 0; r < R; ++r) {
-            int ci = c0 + r * 32 + lane;
-            bool act = ci < len;
-            w[r] = act ? a.wchain[a.chain_off[j] + ci] : Real(0);
-            n[r] = a.band_start[j] + (act ? ci : 0);
-        }
+        // ---- this segment's chain (one wavenumber bin of band j per lane) ----------------------
+        const int ci = c0 + lane;
+        const bool act = ci < a.band_len[j];
+        const Real w = act ? a.wchain[a.chain_off[j] + ci] : Real(0);
+        const int64_t n = a.band_start[j] + (act ? ci : 0);
         if (c0 == 0 && lane == 0) {   // boundary terms: Trans(i,i) = sum of the nu-weights
             bacc_up[L - 1] += (double)bg * a.band_sumw[j];
             bacc_dn[0] += (double)bs * a.band_sumw[j];
         }
-        // ---- downward sweep, TOA -> surface ----------------------------------------------------
-        Real E[R], H[R];
-        Src Icur[R], Inext[R];
+        const int ridx = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+        const bool rlane = (lane & 3) == 0;
+
+        // ---- downward sweep, TOA -> surface, kU layers per block -------------------------------
+        // raw[u][m]: table value (or tau) of interface k0+1+u, loaded one block ahead so the
+        // L2/HBM latency hides behind the previous block's exp and recurrence work.
+        Src raw[kU][MR];
+        auto load_block = [&](int kfirst) {
 #pragma unroll
-        for (int r = 0; r < R; ++r) {
-            E[r] = Real(1);
-            H[r] = Real(0);
-            if (FUSED) {
-                Real acc = Real(0);
-                for (int m = 0; m < M; ++m) acc += qg[m * L] * a.KL[koff[m * L] + n[r]];
-                Icur[r] = (Src)acc;
-                acc = Real(0);
-                for (int m = 0; m < M; ++m) acc += qg[m * L + 1] * a.KL[koff[m * L + 1] + n[r]];
-                Inext[r] = (Src)acc;
-            } else {
-                Icur[r] = (Src)tau_col[n[r]];
-                Inext[r] = (Src)tau_col[a.N + n[r]];
-            }
-        }
-        for (int k = 0; k < nl; ++k) {
-            Src Iload[R];
-            const int kk = (k + 2 < L) ? k + 2 : L - 1;   // prefetch one layer ahead
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
+            for (int u = 0; u < kU; ++u) {
+                const int kk = min(kfirst + u, L - 1);
                 if (FUSED) {
-                    Real acc = Real(0);
-                    for (int m = 0; m < M; ++m) acc += qg[m * L + kk] * a.KL[koff[m * L + kk] + n[r]];
-                    Iload[r] = (Src)acc;
+#pragma unroll
+                    for (int m = 0; m < MR; ++m) raw[u][m] = (Src)a.KL[koff[m * L + kk] + n];
                 } else {
-                    Iload[r] = (Src)tau_col[(int64_t)kk * a.N + n[r]];
+                    raw[u][0] = (Src)tau_col[(int64_t)kk * a.N + n];
                 }
             }
-            const Real dl = lw ? coef[k] : Real(0), dg = lw ? coef[nl + k] : Real(0);
-            const Real hdp = (Real)a.hdP[k];
-            Real v = Real(0);
+        };
+        Src Iprev;
+        if (FUSED) {
+            Real acc = Real(0);
 #pragma unroll
-            for (int r = 0; r < R; ++r) {
-                Real dtau = FUSED ? (Real)(hdp * (Real)(Icur[r] + Inext[r])) : (Real)(Inext[r] - Icur[r]);
-                Real t = exp_neg(dtau);
-                ts[(k * R + r) * 32 + lane] = t;
-                E[r] *= t;
-                Real val = bs * E[r];
-                if (lw) {
-                    Real om = Real(1) - t;
-                    Real S = t * H[r];
-                    val += S + dl * om;
-                    H[r] = S + dg * om;
-                }
-                v += w[r] * val;
-                Icur[r] = Inext[r];
-                Inext[r] = Iload[r];
-            }
-            v = warp_sum(v);
-            if (lane == 0) bacc_dn[k + 1] += (double)v;
+            for (int m = 0; m < MR; ++m) acc += qg[m * L] * a.KL[koff[m * L] + n];
+            Iprev = (Src)acc;
+        } else {
+            Iprev = (Src)tau_col[n];
         }
-        // ---- upward sweep, surface -> TOA -------------------------------------------------------
-        Real S[R];
+        load_block(1);
+        Real E = Real(1), H = Real(0);
+        for (int k0 = 0; k0 < nl; k0 += kU) {
+            Src In[kU];
 #pragma unroll
-        for (int r = 0; r < R; ++r) {
-            E[r] = Real(1);
-            S[r] = Real(0);
-        }
-        for (int i = nl - 1; i >= 0; --i) {
-            const Real uf = lw ? coef[2 * nl + i] : Real(0), ug = lw ? coef[3 * nl + i] : Real(0);
-            Real v = Real(0);
+            for (int u = 0; u < kU; ++u) {
+                if (FUSED) {
+                    const int kk = min(k0 + 1 + u, L - 1);
+                    Real acc = Real(0);
 #pragma unroll
-            for (int r = 0; r < R; ++r) {
-                Real t = ts[(i * R + r) * 32 + lane];
-                E[r] *= t;
-                Real val = bg * E[r];
-                if (lw) {
-                    Real om = Real(1) - t;
-                    Real y = t * S[r];
-                    val += y + uf * om;
-                    S[r] = y + ug * om;
+                    for (int m = 0; m < MR; ++m) acc += qg[m * L + kk] * (Real)raw[u][m];
+                    In[u] = (Src)acc;
+                } else {
+                    In[u] = raw[u][0];
                 }
-                v += w[r] * val;
             }
-            v = warp_sum(v);
-            if (lane == 0) bacc_up[i] += (double)v;
+            load_block(k0 + 1 + kU);
+            Real t[kU];
+#pragma unroll
+            for (int u = 0; u < kU; ++u) {
+                const int k = k0 + u;
+                const Src lo = u ? In[u - 1] : Iprev;
+                Real dtau = FUSED ? (Real)((Real)a.hdP[min(k, nl - 1)] * (Real)(lo + In[u])) : (Real)(In[u] - lo);
+                if (k >= nl) dtau = Real(0);
+                t[u] = exp_neg(dtau);
+                if (k < nl) ts[k * 32 + lane] = t[u];
+            }
+            Iprev = In[kU - 1];
+            Real v[kU];
+#pragma unroll
+            for (int u = 0; u < kU; ++u) {
+                const int k = min(k0 + u, nl - 1);
+                E *= t[u];
+                Real val = bs * E;
+                if (lw) {
+                    const Real om = Real(1) - t[u];
+                    const Real S = t[u] * H;
+                    val += S + coef[k] * om;
+                    H = S + coef[nl + k] * om;
+                }
+                v[u] = w * val;
+            }
+            const Real r = reduce8(v, lane);
+            if (rlane && k0 + ridx < nl) bacc_dn[k0 + ridx + 1] += (double)r;
+        }
+        // ---- upward sweep, surface -> TOA ---------------------------------------------------------
+        E = Real(1);
+        Real S = Real(0);
+        for (int k0 = nl - 1; k0 >= 0; k0 -= kU) {
+            Real t[kU], v[kU];
+#pragma unroll
+            for (int u = 0; u < kU; ++u) t[u] = (k0 - u >= 0) ? ts[(k0 - u) * 32 + lane] : Real(1);
+#pragma unroll
+            for (int u = 0; u < kU; ++u) {
+                const int i = max(k0 - u, 0);
+                E *= t[u];
+                Real val = bg * E;
+                if (lw) {
+                    const Real om = Real(1) - t[u];
+                    const Real y = t[u] * S;
+                    val += y + coef[2 * nl + i] * om;
+                    S = y + coef[3 * nl + i] * om;
+                }
+                v[u] = w * val;
+            }
+            const Real r = reduce8(v, lane);
+            if (rlane && k0 - ridx >= 0) bacc_up[k0 - ridx] += (double)r;
         }
     }
     if (cur >= 0) flush(cur);

@@ -6,7 +6,7 @@
 
 namespace cmb {
 
-constexpr int kMaxMolecules = 8;
+constexpr int kMaxMolecules = 4;
 constexpr int kChains = 1;  // wavenumber bins per lane and pass of the flux kernel (R)
 
 int check_table(const cmb200_table *t);

@@ -171,6 +171,9 @@ int64_t cmb200_launch_count(void);
  * DFMA and FFMA loops (TFLOP/s, 2 flop per FMA) and a device copy (GB/s, read+write). */
 int cmb200_measure_peaks(int device, double *fp64_tflops, double *fp32_tflops, double *copy_gbs);
 
+/* Test hook: the flux kernel's own exp(-x) routine evaluated on n values (HOST pointers). */
+int cmb200_test_exp_neg_host(const double *x, int64_t n, double *out);
+
 #ifdef __cplusplus
 }
 #endif
