@@ -132,13 +132,15 @@ def test_dtransmission_dq(rg):
 
 
 # ---- A6-A9: resident tau ----------------------------------------------------------------------
-def heating_ok(got, ref, net_ref, P, tol):
-    """Heating rate = g/c_p d(net)/dp is a difference of nearly equal net fluxes, so even the
-    reference's own FP64 evaluation carries rounding noise of a few ulp(net)/dp.  Pass when the
-    norm-wise error is below ``tol`` (north_star: 1e-10) or below that intrinsic floor:
-    16 eps max|net| g/c_p / dp per layer."""
+def heating_ok(got, ref, up, dn, delta, P, tol):
+    """Heating rate = g/c_p d(net)/dp with net = sum_j up_j delta_j - sum_j dn_j delta_j: a
+    difference of differences of nearly equal numbers, so even the reference's own FP64
+    evaluation carries rounding noise of a few ulp of those band sums divided by dp.  Pass when
+    the norm-wise error is below ``tol`` (north_star: 1e-10) or below that intrinsic floor,
+    16 eps max(sum_j up_j delta_j) g/c_p / dp per layer."""
     err = np.abs(np.asarray(got) - ref)
-    floor = 16 * np.finfo(float).eps * np.abs(net_ref).max() * orc.g / orc.c_p_dry / np.diff(P)
+    mag = max(np.sum(np.abs(up) * delta, axis=1).max(), np.sum(np.abs(dn) * delta, axis=1).max())
+    floor = 16 * np.finfo(float).eps * mag * orc.g / orc.c_p_dry / np.diff(P)
     return bool(np.all((err <= tol * np.abs(ref).max()) | (err <= floor)))
 
 
@@ -146,7 +148,7 @@ def check_flux(out, c, tol):
     assert relmax(out['up'][0], c['up']) < tol
     assert relmax(out['down'][0], c['down']) < tol
     assert relmax(out['net'][0], c['net']) < tol
-    assert heating_ok(out['heating'][0], c['heating'], c['net'], c['P'], tol)
+    assert heating_ok(out['heating'][0], c['heating'], c['up'], c['down'], c['band_delta'], c['P'], tol)
 
 
 @pytest.mark.parametrize('name', CASES)
@@ -211,7 +213,7 @@ def test_batched_fused_columns_against_oracle(name, n_col):
         assert relmax(out['up'][i], up) < TOL64
         assert relmax(out['down'][i], dn) < TOL64
         assert relmax(out['net'][i], net) < TOL64
-        assert heating_ok(out['heating'][i], heat, net, c['P'], TOL64)
+        assert heating_ok(out['heating'][i], heat, up, dn, c['band_delta'], c['P'], TOL64)
 
 
 def test_whole_column_mode_equals_split_mode():
@@ -306,7 +308,7 @@ def test_properties_larger_grid():
         assert relmax(out['up'][i], up) < TOL64
         assert relmax(out['down'][i], dn) < TOL64
         assert relmax(out['net'][i], net) < TOL64
-        assert heating_ok(out['heating'][i], heat, net, c['P'], TOL64)
+        assert heating_ok(out['heating'][i], heat, up, dn, c['band_delta'], c['P'], TOL64)
 
 
 def test_errors():
