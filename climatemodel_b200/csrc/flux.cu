@@ -65,8 +65,12 @@ static int ensure_partition(cmb200_plan *p, int64_t n_col, int warps_per_cta) {
 template <typename Real, int MM>
 static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *Tint, cudaStream_t s) {
     const int L = p->L;
-    constexpr bool FUSED = MM > 0;
-    const size_t per_warp = flux_warp_smem<Real, FUSED>(L, MM);
+    const size_t per_warp = flux_warp_smem<Real, MM>(L);
+    const double span = MM > 0 ? (double)MM * L * p->nT_pad * (double)p->pitch * sizeof(Real) / 16.0 : (double)L * (double)p->N;
+    if (span >= 4294967296.0) {
+        set_error("table / tau rows exceed the 32-bit row offsets of the flux kernel (%.3g units)", span);
+        return CMB200_ERR_LIMIT;
+    }
     int max_smem = 0;
     CMB_CUDA(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, p->device));
     int warps = (int)std::min<size_t>(8, (size_t)max_smem / per_warp);

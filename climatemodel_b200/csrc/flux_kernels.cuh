@@ -45,58 +45,136 @@ struct FluxArgs {
     double *up, *down, *net, *heating, *scratch;
 };
 
+constexpr int kU = 8;   // layers per block of the sweeps (instruction-level parallelism)
+
+// Per-level, warp-uniform lookup data of one molecule kept in shared memory: q/g and the offset
+// of the table row KL[m][k][tidx] (fused path) or of the tau row k (resident-tau path).  Level k
+// sits at index k + kLevShift so that the kU levels k0+1 .. k0+kU of a block start on a 16-byte
+// boundary and are read with vector loads; levels are padded beyond L-1 with q/g = 0 and a valid
+// offset so that the sweeps need no bounds checks.
+constexpr int kLevShift = 3;
+template <typename Real>
+struct LevelView {
+    const unsigned *off;   // [MR][stride]
+    const Real *qg;        // [MR][stride]
+    int stride;
+    const Real *hdp;       // [Lp]   half layer thickness, 0 in the padding
+    const Real *coef;      // [4][Lp] emission coefficients of the current long-wave band
+};
+
+// kU consecutive, 16-byte aligned shared-memory values -> registers with 128-bit loads.
+template <typename T>
+__device__ __forceinline__ void lds_block(const T *p, T (&o)[kU]) {
+    constexpr int n16 = kU * sizeof(T) / 16;
+    union {
+        uint4 v[n16];
+        T t[kU];
+    } buf;
+#pragma unroll
+    for (int i = 0; i < n16; ++i) buf.v[i] = reinterpret_cast<const uint4 *>(p)[i];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) o[u] = buf.t[u];
+}
+
+__host__ __device__ inline int padded_layers(int L) { return ((L - 1) + kU - 1) / kU * kU; }
+
 // Per-warp shared-memory layout (every sub-array 16-byte aligned).
-template <typename Real, bool FUSED>
+template <typename Real, int MM>
 struct WarpSmem {
-    size_t off_koff, off_qg, off_coef, off_ts, total;
-    __host__ __device__ WarpSmem(int L, int M) {
+    size_t off_nacc, off_off, off_qg, off_hdp, off_coef, off_ts, total;
+    int lev_stride;
+    __host__ __device__ WarpSmem(int L) {
         auto up16 = [](size_t x) { return (x + 15) & ~(size_t)15; };
-        size_t b = up16((size_t)4 * L * sizeof(double));                 // bacc_up/dn, nacc_up/dn
-        off_koff = b;
-        if (FUSED) b = up16(b + (size_t)M * L * sizeof(long long));
+        const int Lp = padded_layers(L), MR = MM > 0 ? MM : 1;
+        size_t b = up16((size_t)2 * (Lp + kU) * sizeof(double));          // bacc_up, bacc_dn
+        off_nacc = b;
+        b = up16(b + (size_t)2 * L * sizeof(double));                     // nacc_up, nacc_dn
+        lev_stride = Lp + 2 * kU;                                         // level k at k + kLevShift
+        off_off = b;
+        b = up16(b + (size_t)MR * lev_stride * sizeof(unsigned));
         off_qg = b;
-        if (FUSED) b = up16(b + (size_t)M * L * sizeof(Real));
+        b = up16(b + (size_t)MR * lev_stride * sizeof(Real));
+        off_hdp = b;
+        b = up16(b + (size_t)Lp * sizeof(Real));
         off_coef = b;
-        b = up16(b + (size_t)4 * (L - 1) * sizeof(Real));
+        b = up16(b + (size_t)4 * Lp * sizeof(Real));
         off_ts = b;
-        size_t ts_bytes = (size_t)(L - 1) * kChains * 32 * sizeof(Real);
-        size_t planck_bytes = (size_t)2 * L * sizeof(double);            // band-prologue scratch
+        size_t ts_bytes = (size_t)Lp * 32 * sizeof(Real);
+        size_t planck_bytes = (size_t)2 * L * sizeof(double);             // band-prologue scratch
         b = up16(b + (ts_bytes > planck_bytes ? ts_bytes : planck_bytes));
         total = b;
     }
 };
-template <typename Real, bool FUSED>
-__host__ __device__ inline size_t flux_warp_smem(int L, int M) {
-    return WarpSmem<Real, FUSED>(L, M).total;
+template <typename Real, int MM>
+__host__ __device__ inline size_t flux_warp_smem(int L) {
+    return WarpSmem<Real, MM>(L).total;
 }
-
-constexpr int kU = 8;   // layers per block of the sweeps (instruction-level parallelism)
 
 // exp(-x) for the layer transmissivity.  FP64: n = rint(-x log2 e), r = -x - n ln2 (two-term
 // Cody-Waite), degree-11 near-minimax polynomial on |r| <= ln2/2 (max rel. error 1.6e-17 before
-// rounding), scaled by 2^n through the exponent field.  Arguments beyond exp(-708) clamp there
-// (3e-308, nothing at the 1e-10 parity level); no other special cases are needed on this path.
+// rounding), scaled by 2^n through the exponent field with n clamped to the normal range: beyond
+// exp(-708) the result is ~1e-308 or less (nothing at the 1e-10 parity level); no other special
+// cases are needed on this path.
+// Coefficients sit in constant memory so that each DFMA takes its constant as an operand.
+__constant__ double kExpC[16] = {
+    2.51100492048186583e-08, 2.76326547225277896e-07, 2.75572408872298695e-06, 2.48014854415613131e-05,
+    1.98412698900764028e-04, 1.38888889523528631e-03, 8.33333333331958900e-03, 4.16666666664879531e-02,
+    1.66666666666666796e-01, 5.00000000000001887e-01, 1.0, 1.4426950408889634074,
+    6755399441055744.0 /* 1.5 * 2^52 */, -6.93147180369123816490e-01, -1.90821492927058770002e-10, 0.0};
+
+// Optical thicknesses beyond 1e4 (exp(-x) = 0 in FP64 long before) are clamped through the high
+// word, one integer min, so that the range reduction below never sees huge arguments.
+__device__ __forceinline__ double clamp_thickness(double x) {
+    return __hiloint2double(min(__double2hiint(x), 0x40C38800), __double2loint(x));
+}
 __device__ __forceinline__ double exp_neg(double x) {
-    double y = fmin(fmax(-x, -708.0), 709.0);
-    const double shifter = 6755399441055744.0;                 // 1.5 * 2^52
-    double tn = fma(y, 1.4426950408889634074, shifter);
-    const int n = __double2loint(tn);
-    tn -= shifter;
-    double r = fma(tn, -6.93147180369123816490e-01, y);
-    r = fma(tn, -1.90821492927058770002e-10, r);
-    double p = 2.51100492048186583e-08;
-    p = fma(p, r, 2.76326547225277896e-07);
-    p = fma(p, r, 2.75572408872298695e-06);
-    p = fma(p, r, 2.48014854415613131e-05);
-    p = fma(p, r, 1.98412698900764028e-04);
-    p = fma(p, r, 1.38888889523528631e-03);
-    p = fma(p, r, 8.33333333331958900e-03);
-    p = fma(p, r, 4.16666666664879531e-02);
-    p = fma(p, r, 1.66666666666666796e-01);
-    p = fma(p, r, 5.00000000000001887e-01);
-    p = fma(p, r, 1.0);
-    p = fma(p, r, 1.0);
+    const double y = -clamp_thickness(x);
+    double tn = fma(y, kExpC[11], kExpC[12]);
+    const int n = max(min(__double2loint(tn), 1023), -1022);   // 2^n stays a normal number
+    tn -= kExpC[12];
+    double r = fma(tn, kExpC[13], y);
+    r = fma(tn, kExpC[14], r);
+    double p = kExpC[0];
+#pragma unroll
+    for (int i = 1; i <= 10; ++i) p = fma(p, r, kExpC[i]);
+    p = fma(p, r, kExpC[10]);
     return __hiloint2double(__double2hiint(p) + (n << 20), __double2loint(p));
+}
+// The same for kU values at once, written step-by-step across the values so that the kU
+// independent dependency chains are adjacent in program order and the FP64 pipe stays busy.
+__device__ __forceinline__ void exp_neg_block(const double (&xin)[kU], double (&out)[kU]) {
+    double x[kU], tn[kU], r[kU], p[kU];
+    int n[kU];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+        x[u] = clamp_thickness(xin[u]);
+        tn[u] = fma(-x[u], kExpC[11], kExpC[12]);
+    }
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+        n[u] = max(min(__double2loint(tn[u]), 1023), -1022);
+        tn[u] -= kExpC[12];
+    }
+#pragma unroll
+    for (int u = 0; u < kU; ++u) r[u] = fma(tn[u], kExpC[13], -x[u]);
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+        r[u] = fma(tn[u], kExpC[14], r[u]);
+        p[u] = kExpC[0];
+    }
+#pragma unroll
+    for (int i = 1; i <= 10; ++i)
+#pragma unroll
+        for (int u = 0; u < kU; ++u) p[u] = fma(p[u], r[u], kExpC[i]);
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+        p[u] = fma(p[u], r[u], kExpC[10]);
+        out[u] = __hiloint2double(__double2hiint(p[u]) + (n[u] << 20), __double2loint(p[u]));
+    }
+}
+__device__ __forceinline__ void exp_neg_block(const float (&x)[kU], float (&out)[kU]) {
+#pragma unroll
+    for (int u = 0; u < kU; ++u) out[u] = __expf(-x[u]);
 }
 __device__ __forceinline__ float exp_neg(float x) { return __expf(-x); }
 
@@ -126,6 +204,118 @@ __device__ __forceinline__ Real reduce8(const Real (&v)[8], int lane) {
     return c;
 }
 
+// One direction pair of sweeps for the chain held by this lane.  LW selects the long-wave
+// variant (emission recurrences); MM as in flux_kernel.
+//   down, TOA -> surface:  t_k = exp(-dtau_k);  E <- E t_k;  value at interface k+1
+//   up,   surface -> TOA:  replay t_k from shared memory;    value at interface k
+// The nu-weight w (and the boundary source) is folded into the initial state so that the values
+// handed to the warp reduction are already weighted.
+template <typename Real, int MM, bool LW>
+__device__ __forceinline__ void sweep_chain(const int lane, const int nl, const int Lp, const Real w, const Real bs, const Real bg,
+                                            const void *src_lane, const LevelView<Real> lv, Real *ts, double *bacc_up,
+                                            double *bacc_dn) {
+    constexpr bool FUSED = MM > 0;
+    constexpr int MR = MM > 0 ? MM : 1;
+    using Src = typename std::conditional<FUSED, Real, double>::type;
+    const char *src_bytes = (const char *)src_lane;
+    constexpr unsigned kOffUnit = FUSED ? 16u : 8u;   // table rows are 64-byte aligned, tau rows only 8
+    const int ridx = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+    const bool rlane = (lane & 3) == 0;
+
+    // raw[u][m]: table value (or tau) of interface k0+1+u, loaded one block ahead so the L2/HBM
+    // latency hides behind the previous block's exp and recurrence work.
+    const Real *hdp = lv.hdp, *coef = lv.coef;
+    Src raw[kU][MR];
+    auto load_block = [&](int kfirst) {      // kfirst = k0 + 1, k0 a multiple of kU
+#pragma unroll
+        for (int m = 0; m < MR; ++m) {
+            unsigned off[kU];
+            lds_block(lv.off + m * lv.stride + kfirst + kLevShift, off);
+#pragma unroll
+            for (int u = 0; u < kU; ++u) raw[u][m] = *(const Src *)(src_bytes + (size_t)off[u] * kOffUnit);
+        }
+    };
+    Src Iprev;
+    if (FUSED) {
+        Real acc = Real(0);
+#pragma unroll
+        for (int m = 0; m < MR; ++m)
+            acc += lv.qg[m * lv.stride + kLevShift] * (Real)(*(const Src *)(src_bytes + (size_t)lv.off[m * lv.stride + kLevShift] * kOffUnit));
+        Iprev = (Src)acc;
+    } else {
+        Iprev = *(const Src *)(src_bytes + (size_t)lv.off[kLevShift] * kOffUnit);
+    }
+    load_block(1);
+    Real E = w * bs, H = Real(0);
+    for (int k0 = 0; k0 < Lp; k0 += kU) {
+        Src In[kU];
+        if (FUSED) {
+            Real qg[kU], acc[kU];
+            lds_block(lv.qg + k0 + 1 + kLevShift, qg);
+#pragma unroll
+            for (int u = 0; u < kU; ++u) acc[u] = qg[u] * (Real)raw[u][0];
+#pragma unroll
+            for (int m = 1; m < MR; ++m) {
+                lds_block(lv.qg + m * lv.stride + k0 + 1 + kLevShift, qg);
+#pragma unroll
+                for (int u = 0; u < kU; ++u) acc[u] = fma(qg[u], (Real)raw[u][m], acc[u]);
+            }
+#pragma unroll
+            for (int u = 0; u < kU; ++u) In[u] = (Src)acc[u];
+        } else {
+#pragma unroll
+            for (int u = 0; u < kU; ++u) In[u] = raw[u][0];
+        }
+        if (k0 + kU < Lp) load_block(k0 + 1 + kU);
+        Real dtau[kU], t[kU], v[kU], hd[kU];
+        if (FUSED) lds_block(hdp + k0, hd);
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+            const Src lo = u ? In[u - 1] : Iprev;
+            dtau[u] = FUSED ? (Real)(hd[u] * (Real)(lo + In[u])) : (Real)(In[u] - lo);
+        }
+        exp_neg_block(dtau, t);
+#pragma unroll
+        for (int u = 0; u < kU; ++u) ts[(k0 + u) * 32 + lane] = t[u];
+        Iprev = In[kU - 1];
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+            E *= t[u];
+            if (LW) {
+                const Real om = fma(-w, t[u], w);              // w (1 - t)
+                const Real S = t[u] * H;
+                v[u] = E + S + coef[k0 + u] * om;
+                H = fma(coef[Lp + k0 + u], om, S);
+            } else {
+                v[u] = E;
+            }
+        }
+        const Real r = reduce8(v, lane);
+        if (rlane && k0 + ridx < nl) bacc_dn[k0 + ridx + 1] += (double)r;
+    }
+    E = w * bg;
+    Real S = Real(0);
+    for (int k0 = Lp - kU; k0 >= 0; k0 -= kU) {
+        Real t[kU], v[kU];
+#pragma unroll
+        for (int u = 0; u < kU; ++u) t[u] = ts[(k0 + u) * 32 + lane];
+#pragma unroll
+        for (int u = kU - 1; u >= 0; --u) {
+            E *= t[u];
+            if (LW) {
+                const Real om = fma(-w, t[u], w);
+                const Real y = t[u] * S;
+                v[u] = E + y + coef[2 * Lp + k0 + u] * om;
+                S = fma(coef[3 * Lp + k0 + u], om, y);
+            } else {
+                v[u] = E;
+            }
+        }
+        const Real r = reduce8(v, lane);
+        if (rlane && k0 + ridx < nl) bacc_up[k0 + ridx] += (double)r;
+    }
+}
+
 // MM = number of molecules of the table-fused path (compile-time so the prefetched table values
 // live in registers); MM = 0 selects the resident-tau path.
 template <typename Real, int MM>
@@ -133,22 +323,23 @@ __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr bool FUSED = MM > 0;
     constexpr int MR = MM > 0 ? MM : 1;
-    using Src = typename std::conditional<FUSED, Real, double>::type;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int L = a.L, nl = a.L - 1, M = MM;
+    const int L = a.L, nl = a.L - 1, Lp = padded_layers(a.L), LS = Lp + kU;
     const int64_t task = (int64_t)blockIdx.x * (blockDim.x >> 5) + warp;
     if (task >= a.n_col * a.parts) return;
     const int64_t col = task / a.parts;
     const int part = (int)(task % a.parts);
 
-    const WarpSmem<Real, FUSED> lay(L, M);
+    const WarpSmem<Real, MM> lay(L);
     unsigned char *base = smem_raw + (size_t)warp * lay.total;
     double *bacc_up = (double *)base;
-    double *bacc_dn = bacc_up + L;
-    double *nacc_up = bacc_dn + L;
+    double *bacc_dn = bacc_up + LS;
+    double *nacc_up = (double *)(base + lay.off_nacc);
     double *nacc_dn = nacc_up + L;
-    long long *koff = (long long *)(base + lay.off_koff);
-    Real *qg = (Real *)(base + lay.off_qg);
+    unsigned *lev_off = (unsigned *)(base + lay.off_off);
+    Real *lev_qg = (Real *)(base + lay.off_qg);
+    const int lstride = lay.lev_stride;
+    Real *hdp = (Real *)(base + lay.off_hdp);
     Real *coef = (Real *)(base + lay.off_coef);
     Real *ts = (Real *)(base + lay.off_ts);
 
@@ -156,18 +347,23 @@ __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
     const double albedo = a.albedo ? a.albedo[col] : a.albedo_scalar;
     const double solar = a.star_geom * (1.0 - albedo) / 4.0;  // (R*/d)^2 (1-albedo)/4, :640-642
 
-    for (int i = lane; i < 4 * L; i += 32) bacc_up[i] = 0.0;
-    const double *tau_col = nullptr;
-    if (FUSED) {
-        for (int idx = lane; idx < M * L; idx += 32) {
-            int m = idx / L, k = idx - m * L;
-            int t = a.tidx[((int64_t)m * a.n_col + col) * L + k];
-            koff[idx] = (((long long)m * L + k) * a.nT_pad + t) * a.pitch;
-            qg[idx] = (Real)(a.q[m * a.q_mol_stride + col * a.q_col_stride + k] / a.g);
+    for (int i = lane; i < 2 * LS; i += 32) bacc_up[i] = 0.0;
+    for (int i = lane; i < 2 * L; i += 32) nacc_up[i] = 0.0;
+    for (int i = lane; i < 4 * Lp; i += 32) coef[i] = Real(0);
+    for (int k = lane; k < Lp; k += 32) hdp[k] = k < nl ? (Real)a.hdP[k] : Real(0);
+    for (int idx = lane; idx < MR * lstride; idx += 32) {
+        const int m = idx / lstride, k = idx - m * lstride - kLevShift, kc = min(max(k, 0), L - 1);
+        if (FUSED) {
+            const int t = a.tidx[((int64_t)m * a.n_col + col) * L + kc];
+            lev_off[idx] = (unsigned)(((((int64_t)m * L + kc) * a.nT_pad + t) * a.pitch * sizeof(Real)) >> 4);
+            lev_qg[idx] = (k >= 0 && k < L) ? (Real)(a.q[m * a.q_mol_stride + col * a.q_col_stride + k] / a.g) : Real(0);
+        } else {
+            lev_off[idx] = (unsigned)((int64_t)kc * a.N);
+            lev_qg[idx] = Real(0);
         }
-    } else {
-        tau_col = a.tau + (int64_t)(a.tau_id ? a.tau_id[col] : 0) * L * a.N;
     }
+    const LevelView<Real> lv{lev_off, lev_qg, lstride, hdp, coef};
+    const double *tau_col = FUSED ? nullptr : a.tau + (int64_t)(a.tau_id ? a.tau_id[col] : 0) * L * a.N;
     __syncwarp();
 
     const int s0 = a.part_seg0[part], s1 = a.part_seg0[part + 1];
@@ -186,8 +382,6 @@ __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
                 if (a.down) a.down[(col * L + i) * a.B + j] = d;
                 nacc_up[i] += u * dj;
                 nacc_dn[i] += d * dj;
-                bacc_up[i] = 0.0;
-                bacc_dn[i] = 0.0;
             }
         } else {
             ++slot;
@@ -195,10 +389,10 @@ __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
             for (int i = lane; i < L; i += 32) {
                 o[i] = bacc_up[i];
                 o[L + i] = bacc_dn[i];
-                bacc_up[i] = 0.0;
-                bacc_dn[i] = 0.0;
             }
         }
+        __syncwarp();
+        for (int i = lane; i < 2 * LS; i += 32) bacc_up[i] = 0.0;
         __syncwarp();
     };
 
@@ -224,10 +418,10 @@ __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
                 for (int k = lane; k < nl; k += 32) {
                     const double bi0 = sbi[k], bi1 = sbi[k + 1], bc = sbc[k];
                     const double *g0 = a.geo + k;
-                    coef[k] = (Real)(g0[0] * bi0 + g0[nl] * bc + g0[2 * nl] * bi1);            // dn_last
-                    coef[nl + k] = (Real)(g0[3 * nl] * bi0 + g0[4 * nl] * bc);                 // dn_gen
-                    coef[2 * nl + k] = (Real)(g0[5 * nl] * bi0 + g0[6 * nl] * bc + g0[7 * nl] * bi1);  // up_first
-                    coef[3 * nl + k] = (Real)(g0[8 * nl] * bc + g0[9 * nl] * bi1);             // up_gen
+                    coef[k] = (Real)(g0[0] * bi0 + g0[nl] * bc + g0[2 * nl] * bi1);                 // dn_last
+                    coef[Lp + k] = (Real)(g0[3 * nl] * bi0 + g0[4 * nl] * bc);                      // dn_gen
+                    coef[2 * Lp + k] = (Real)(g0[5 * nl] * bi0 + g0[6 * nl] * bc + g0[7 * nl] * bi1);   // up_first
+                    coef[3 * Lp + k] = (Real)(g0[8 * nl] * bc + g0[9 * nl] * bi1);                  // up_gen
                 }
                 __syncwarp();
             }
@@ -241,102 +435,11 @@ __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
             bacc_up[L - 1] += (double)bg * a.band_sumw[j];
             bacc_dn[0] += (double)bs * a.band_sumw[j];
         }
-        const int ridx = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
-        const bool rlane = (lane & 3) == 0;
-
-        // ---- downward sweep, TOA -> surface, kU layers per block -------------------------------
-        // raw[u][m]: table value (or tau) of interface k0+1+u, loaded one block ahead so the
-        // L2/HBM latency hides behind the previous block's exp and recurrence work.
-        Src raw[kU][MR];
-        auto load_block = [&](int kfirst) {
-#pragma unroll
-            for (int u = 0; u < kU; ++u) {
-                const int kk = min(kfirst + u, L - 1);
-                if (FUSED) {
-#pragma unroll
-                    for (int m = 0; m < MR; ++m) raw[u][m] = (Src)a.KL[koff[m * L + kk] + n];
-                } else {
-                    raw[u][0] = (Src)tau_col[(int64_t)kk * a.N + n];
-                }
-            }
-        };
-        Src Iprev;
-        if (FUSED) {
-            Real acc = Real(0);
-#pragma unroll
-            for (int m = 0; m < MR; ++m) acc += qg[m * L] * a.KL[koff[m * L] + n];
-            Iprev = (Src)acc;
-        } else {
-            Iprev = (Src)tau_col[n];
-        }
-        load_block(1);
-        Real E = Real(1), H = Real(0);
-        for (int k0 = 0; k0 < nl; k0 += kU) {
-            Src In[kU];
-#pragma unroll
-            for (int u = 0; u < kU; ++u) {
-                if (FUSED) {
-                    const int kk = min(k0 + 1 + u, L - 1);
-                    Real acc = Real(0);
-#pragma unroll
-                    for (int m = 0; m < MR; ++m) acc += qg[m * L + kk] * (Real)raw[u][m];
-                    In[u] = (Src)acc;
-                } else {
-                    In[u] = raw[u][0];
-                }
-            }
-            load_block(k0 + 1 + kU);
-            Real t[kU];
-#pragma unroll
-            for (int u = 0; u < kU; ++u) {
-                const int k = k0 + u;
-                const Src lo = u ? In[u - 1] : Iprev;
-                Real dtau = FUSED ? (Real)((Real)a.hdP[min(k, nl - 1)] * (Real)(lo + In[u])) : (Real)(In[u] - lo);
-                if (k >= nl) dtau = Real(0);
-                t[u] = exp_neg(dtau);
-                if (k < nl) ts[k * 32 + lane] = t[u];
-            }
-            Iprev = In[kU - 1];
-            Real v[kU];
-#pragma unroll
-            for (int u = 0; u < kU; ++u) {
-                const int k = min(k0 + u, nl - 1);
-                E *= t[u];
-                Real val = bs * E;
-                if (lw) {
-                    const Real om = Real(1) - t[u];
-                    const Real S = t[u] * H;
-                    val += S + coef[k] * om;
-                    H = S + coef[nl + k] * om;
-                }
-                v[u] = w * val;
-            }
-            const Real r = reduce8(v, lane);
-            if (rlane && k0 + ridx < nl) bacc_dn[k0 + ridx + 1] += (double)r;
-        }
-        // ---- upward sweep, surface -> TOA ---------------------------------------------------------
-        E = Real(1);
-        Real S = Real(0);
-        for (int k0 = nl - 1; k0 >= 0; k0 -= kU) {
-            Real t[kU], v[kU];
-#pragma unroll
-            for (int u = 0; u < kU; ++u) t[u] = (k0 - u >= 0) ? ts[(k0 - u) * 32 + lane] : Real(1);
-#pragma unroll
-            for (int u = 0; u < kU; ++u) {
-                const int i = max(k0 - u, 0);
-                E *= t[u];
-                Real val = bg * E;
-                if (lw) {
-                    const Real om = Real(1) - t[u];
-                    const Real y = t[u] * S;
-                    val += y + coef[2 * nl + i] * om;
-                    S = y + coef[3 * nl + i] * om;
-                }
-                v[u] = w * val;
-            }
-            const Real r = reduce8(v, lane);
-            if (rlane && k0 - ridx >= 0) bacc_up[k0 - ridx] += (double)r;
-        }
+        const void *src_lane = FUSED ? (const void *)(a.KL + n) : (const void *)(tau_col + n);
+        if (lw)
+            sweep_chain<Real, MM, true>(lane, nl, Lp, w, bs, bg, src_lane, lv, ts, bacc_up, bacc_dn);
+        else
+            sweep_chain<Real, MM, false>(lane, nl, Lp, w, bs, bg, src_lane, lv, ts, bacc_up, bacc_dn);
     }
     if (cur >= 0) flush(cur);
 
