@@ -112,9 +112,7 @@ __host__ __device__ inline size_t flux_warp_smem(int L) {
 
 // exp(-x) for the layer transmissivity.  FP64: n = rint(-x log2 e), r = -x - n ln2 (two-term
 // Cody-Waite), degree-11 near-minimax polynomial on |r| <= ln2/2 (max rel. error 1.6e-17 before
-// rounding), scaled by 2^n through the exponent field with n clamped to the normal range: beyond
-// exp(-708) the result is ~1e-308 or less (nothing at the 1e-10 parity level); no other special
-// cases are needed on this path.
+// rounding), scaled by 2^n through the exponent field; no special cases beyond the argument clamp.
 // Coefficients sit in constant memory so that each DFMA takes its constant as an operand.
 __constant__ double kExpC[16] = {
     2.51100492048186583e-08, 2.76326547225277896e-07, 2.75572408872298695e-06, 2.48014854415613131e-05,
@@ -122,15 +120,16 @@ __constant__ double kExpC[16] = {
     1.66666666666666796e-01, 5.00000000000001887e-01, 1.0, 1.4426950408889634074,
     6755399441055744.0 /* 1.5 * 2^52 */, -6.93147180369123816490e-01, -1.90821492927058770002e-10, 0.0};
 
-// Optical thicknesses beyond 1e4 (exp(-x) = 0 in FP64 long before) are clamped through the high
-// word, one integer min, so that the range reduction below never sees huge arguments.
+// Optical thicknesses beyond 708 (exp(-708) = 3e-308, nothing at the 1e-10 parity level) are
+// clamped through the high word -- one integer min -- so that 2^n below stays a normal number
+// and the range reduction never sees huge arguments.  (Layer thicknesses are >= 0 on this path.)
 __device__ __forceinline__ double clamp_thickness(double x) {
-    return __hiloint2double(min(__double2hiint(x), 0x40C38800), __double2loint(x));
+    return __hiloint2double(min(__double2hiint(x), 0x40862000), __double2loint(x));
 }
 __device__ __forceinline__ double exp_neg(double x) {
     const double y = -clamp_thickness(x);
     double tn = fma(y, kExpC[11], kExpC[12]);
-    const int n = max(min(__double2loint(tn), 1023), -1022);   // 2^n stays a normal number
+    const int n = __double2loint(tn);
     tn -= kExpC[12];
     double r = fma(tn, kExpC[13], y);
     r = fma(tn, kExpC[14], r);
@@ -152,7 +151,7 @@ __device__ __forceinline__ void exp_neg_block(const double (&xin)[kU], double (&
     }
 #pragma unroll
     for (int u = 0; u < kU; ++u) {
-        n[u] = max(min(__double2loint(tn[u]), 1023), -1022);
+        n[u] = __double2loint(tn[u]);
         tn[u] -= kExpC[12];
     }
 #pragma unroll
@@ -210,21 +209,30 @@ __device__ __forceinline__ Real reduce8(const Real (&v)[8], int lane) {
 //   up,   surface -> TOA:  replay t_k from shared memory;    value at interface k
 // The nu-weight w (and the boundary source) is folded into the initial state so that the values
 // handed to the warp reduction are already weighted.
+//
+// Both sweeps are software-pipelined by hand over blocks of kU layers, because a lane's work is
+// one long dependency chain and only ~1.5 warps per scheduler fit next to the t-store: while the
+// kU independent exp evaluations of block b are in flight (stage A), the serial recurrence of
+// block b-1 (stage B) and its warp reduction (stage C) are issued in between, statement by
+// statement -- ptxas keeps this order, so the FP64 pipe always has independent work.
 template <typename Real, int MM, bool LW>
-__device__ __forceinline__ void sweep_chain(const int lane, const int nl, const int Lp, const Real w, const Real bs, const Real bg,
-                                            const void *src_lane, const LevelView<Real> lv, Real *ts, double *bacc_up,
-                                            double *bacc_dn) {
+__device__ __forceinline__ void sweep_chain(const int lane, const int nl, const int Lp, const Real w, const Real bs,
+                                            const Real bg, const void *src_lane, const LevelView<Real> lv, Real *ts,
+                                            double *bacc_up, double *bacc_dn) {
     constexpr bool FUSED = MM > 0;
     constexpr int MR = MM > 0 ? MM : 1;
+    constexpr bool F64 = sizeof(Real) == 8;
     using Src = typename std::conditional<FUSED, Real, double>::type;
     const char *src_bytes = (const char *)src_lane;
     constexpr unsigned kOffUnit = FUSED ? 16u : 8u;   // table rows are 64-byte aligned, tau rows only 8
+    const unsigned full = 0xffffffffu;
+    const bool h4 = lane & 16, h3 = lane & 8, h2 = lane & 4;
     const int ridx = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
     const bool rlane = (lane & 3) == 0;
+    const Real *hdp = lv.hdp, *coef = lv.coef;
 
     // raw[u][m]: table value (or tau) of interface k0+1+u, loaded one block ahead so the L2/HBM
-    // latency hides behind the previous block's exp and recurrence work.
-    const Real *hdp = lv.hdp, *coef = lv.coef;
+    // latency hides behind the previous block's work.
     Src raw[kU][MR];
     auto load_block = [&](int kfirst) {      // kfirst = k0 + 1, k0 a multiple of kU
 #pragma unroll
@@ -246,74 +254,205 @@ __device__ __forceinline__ void sweep_chain(const int lane, const int nl, const 
         Iprev = *(const Src *)(src_bytes + (size_t)lv.off[kLevShift] * kOffUnit);
     }
     load_block(1);
-    Real E = w * bs, H = Real(0);
-    for (int k0 = 0; k0 < Lp; k0 += kU) {
-        Src In[kU];
-        if (FUSED) {
-            Real qg[kU], acc[kU];
-            lds_block(lv.qg + k0 + 1 + kLevShift, qg);
+
+    // ---- shared pieces of the pipeline stages -----------------------------------------------------
+    Real E, H, tp[kU], v[kU], a4[4], a2[2], c1;      // recurrence state, block b-1's t and values
+    auto C1 = [&]() {
 #pragma unroll
-            for (int u = 0; u < kU; ++u) acc[u] = qg[u] * (Real)raw[u][0];
+        for (int i = 0; i < 4; ++i) {
+            const Real keep = h4 ? v[i + 4] : v[i], send = h4 ? v[i] : v[i + 4];
+            a4[i] = keep + __shfl_xor_sync(full, send, 16);
+        }
+    };
+    auto C2 = [&]() {
 #pragma unroll
-            for (int m = 1; m < MR; ++m) {
-                lds_block(lv.qg + m * lv.stride + k0 + 1 + kLevShift, qg);
-#pragma unroll
-                for (int u = 0; u < kU; ++u) acc[u] = fma(qg[u], (Real)raw[u][m], acc[u]);
-            }
-#pragma unroll
-            for (int u = 0; u < kU; ++u) In[u] = (Src)acc[u];
+        for (int i = 0; i < 2; ++i) {
+            const Real keep = h3 ? a4[i + 2] : a4[i], send = h3 ? a4[i] : a4[i + 2];
+            a2[i] = keep + __shfl_xor_sync(full, send, 8);
+        }
+    };
+    auto C3 = [&]() {
+        const Real keep = h2 ? a2[1] : a2[0], send = h2 ? a2[0] : a2[1];
+        c1 = keep + __shfl_xor_sync(full, send, 4);
+    };
+    auto C4 = [&]() { c1 += __shfl_xor_sync(full, c1, 2); };
+    auto C5 = [&]() { c1 += __shfl_xor_sync(full, c1, 1); };
+
+    // ---- downward sweep ---------------------------------------------------------------------------------
+    auto Bdn = [&](int kb, int u) {           // recurrence step of layer kb+u (block b-1)
+        E *= tp[u];
+        if (LW) {
+            const Real om = fma(-w, tp[u], w);              // w (1 - t)
+            const Real S = tp[u] * H;
+            v[u] = E + S + coef[kb + u] * om;
+            H = fma(coef[Lp + kb + u], om, S);
         } else {
-#pragma unroll
-            for (int u = 0; u < kU; ++u) In[u] = raw[u][0];
+            v[u] = E;
         }
-        if (k0 + kU < Lp) load_block(k0 + 1 + kU);
-        Real dtau[kU], t[kU], v[kU], hd[kU];
-        if (FUSED) lds_block(hdp + k0, hd);
+    };
+    auto down_iter = [&](auto doA_t, auto doB_t, const int k0) {
+        constexpr bool DO_A = decltype(doA_t)::value, DO_B = decltype(doB_t)::value;
+        const int kb = k0 - kU;
+        Real x[kU], t[kU];
+        // stage A set-up: layer integrand of the block's interfaces, next block's loads, dtau
+        if (DO_A) {
+            Src In[kU];
+            if (FUSED) {
+                Real qg[kU], acc[kU];
+                lds_block(lv.qg + k0 + 1 + kLevShift, qg);
 #pragma unroll
-        for (int u = 0; u < kU; ++u) {
-            const Src lo = u ? In[u - 1] : Iprev;
-            dtau[u] = FUSED ? (Real)(hd[u] * (Real)(lo + In[u])) : (Real)(In[u] - lo);
-        }
-        exp_neg_block(dtau, t);
+                for (int u = 0; u < kU; ++u) acc[u] = qg[u] * (Real)raw[u][0];
 #pragma unroll
-        for (int u = 0; u < kU; ++u) ts[(k0 + u) * 32 + lane] = t[u];
-        Iprev = In[kU - 1];
+                for (int m = 1; m < MR; ++m) {
+                    lds_block(lv.qg + m * lv.stride + k0 + 1 + kLevShift, qg);
 #pragma unroll
-        for (int u = 0; u < kU; ++u) {
-            E *= t[u];
-            if (LW) {
-                const Real om = fma(-w, t[u], w);              // w (1 - t)
-                const Real S = t[u] * H;
-                v[u] = E + S + coef[k0 + u] * om;
-                H = fma(coef[Lp + k0 + u], om, S);
+                    for (int u = 0; u < kU; ++u) acc[u] = fma(qg[u], (Real)raw[u][m], acc[u]);
+                }
+#pragma unroll
+                for (int u = 0; u < kU; ++u) In[u] = (Src)acc[u];
             } else {
-                v[u] = E;
+#pragma unroll
+                for (int u = 0; u < kU; ++u) In[u] = raw[u][0];
+            }
+            if (k0 + kU < Lp) load_block(k0 + 1 + kU);
+            Real hd[kU];
+            if (FUSED) lds_block(hdp + k0, hd);
+#pragma unroll
+            for (int u = 0; u < kU; ++u) {
+                const Src lo = u ? In[u - 1] : Iprev;
+                x[u] = FUSED ? (Real)(hd[u] * (Real)(lo + In[u])) : (Real)(In[u] - lo);
+            }
+            Iprev = In[kU - 1];
+        }
+        if constexpr (F64) {
+            double tn[kU], r[kU], p[kU];
+            int n[kU];
+            if (DO_A) {
+#pragma unroll
+                for (int u = 0; u < kU; ++u) {
+                    x[u] = clamp_thickness(x[u]);
+                    tn[u] = fma(-x[u], kExpC[11], kExpC[12]);
+                }
+            }
+            if (DO_B) { Bdn(kb, 0); Bdn(kb, 1); }
+            if (DO_A) {
+#pragma unroll
+                for (int u = 0; u < kU; ++u) {
+                    n[u] = __double2loint(tn[u]);
+                    tn[u] -= kExpC[12];
+                }
+            }
+            if (DO_B) { Bdn(kb, 2); Bdn(kb, 3); }
+            if (DO_A) {
+#pragma unroll
+                for (int u = 0; u < kU; ++u) r[u] = fma(tn[u], kExpC[13], -x[u]);
+            }
+            if (DO_B) { Bdn(kb, 4); Bdn(kb, 5); }
+            if (DO_A) {
+#pragma unroll
+                for (int u = 0; u < kU; ++u) {
+                    r[u] = fma(tn[u], kExpC[14], r[u]);
+                    p[u] = kExpC[0];
+                }
+            }
+            if (DO_B) { Bdn(kb, 6); Bdn(kb, 7); }
+#pragma unroll
+            for (int i = 1; i <= 10; ++i) {
+                if (DO_A) {
+#pragma unroll
+                    for (int u = 0; u < kU; ++u) p[u] = fma(p[u], r[u], kExpC[i]);
+                }
+                if (DO_B) {
+                    if (i == 1) C1();
+                    if (i == 3) C2();
+                    if (i == 5) C3();
+                    if (i == 7) C4();
+                    if (i == 9) C5();
+                }
+            }
+            if (DO_A) {
+#pragma unroll
+                for (int u = 0; u < kU; ++u) {
+                    p[u] = fma(p[u], r[u], kExpC[10]);
+                    t[u] = __hiloint2double(__double2hiint(p[u]) + (n[u] << 20), __double2loint(p[u]));
+                }
+            }
+        } else {
+            if (DO_A) {
+#pragma unroll
+                for (int u = 0; u < kU; ++u) t[u] = exp_neg(x[u]);
+            }
+            if (DO_B) {
+#pragma unroll
+                for (int u = 0; u < kU; ++u) Bdn(kb, u);
+                C1(); C2(); C3(); C4(); C5();
             }
         }
-        const Real r = reduce8(v, lane);
-        if (rlane && k0 + ridx < nl) bacc_dn[k0 + ridx + 1] += (double)r;
-    }
+        if (DO_B) {
+            if (rlane && kb + ridx < nl) bacc_dn[kb + ridx + 1] += (double)c1;
+        }
+        if (DO_A) {
+#pragma unroll
+            for (int u = 0; u < kU; ++u) {
+                ts[(k0 + u) * 32 + lane] = t[u];
+                tp[u] = t[u];
+            }
+        }
+    };
+    E = w * bs;
+    H = Real(0);
+    down_iter(std::true_type{}, std::false_type{}, 0);
+    for (int k0 = kU; k0 < Lp; k0 += kU) down_iter(std::true_type{}, std::true_type{}, k0);
+    down_iter(std::false_type{}, std::true_type{}, Lp);
+
+    // ---- upward sweep: recurrence of block b interleaved with the reduction of block b+1 ------------
+    Real S = Real(0), tn8[kU], vp[kU];
+    auto Bup = [&](int kb, int u) {
+        E *= tp[u];
+        if (LW) {
+            const Real om = fma(-w, tp[u], w);
+            const Real y = tp[u] * S;
+            vp[u] = E + y + coef[2 * Lp + kb + u] * om;
+            S = fma(coef[3 * Lp + kb + u], om, y);
+        } else {
+            vp[u] = E;
+        }
+    };
+    auto up_iter = [&](auto doB_t, auto doC_t, const int k0) {
+        constexpr bool DO_B = decltype(doB_t)::value, DO_C = decltype(doC_t)::value;
+        // prefetch t of the block after this one (k0 - kU) while this block's chain runs
+        if (DO_B && k0 >= kU) {
+#pragma unroll
+            for (int u = 0; u < kU; ++u) tn8[u] = ts[(k0 - kU + u) * 32 + lane];
+        }
+        if (DO_B) Bup(k0, 7);
+        if (DO_C) C1();
+        if (DO_B) { Bup(k0, 6); Bup(k0, 5); }
+        if (DO_C) C2();
+        if (DO_B) { Bup(k0, 4); Bup(k0, 3); }
+        if (DO_C) C3();
+        if (DO_B) Bup(k0, 2);
+        if (DO_C) C4();
+        if (DO_B) { Bup(k0, 1); Bup(k0, 0); }
+        if (DO_C) {
+            C5();
+            const int kc = k0 + kU;
+            if (rlane && kc + ridx < nl) bacc_up[kc + ridx] += (double)c1;
+        }
+        if (DO_B) {
+#pragma unroll
+            for (int u = 0; u < kU; ++u) {
+                v[u] = vp[u];
+                tp[u] = tn8[u];
+            }
+        }
+    };
     E = w * bg;
-    Real S = Real(0);
-    for (int k0 = Lp - kU; k0 >= 0; k0 -= kU) {
-        Real t[kU], v[kU];
 #pragma unroll
-        for (int u = 0; u < kU; ++u) t[u] = ts[(k0 + u) * 32 + lane];
-#pragma unroll
-        for (int u = kU - 1; u >= 0; --u) {
-            E *= t[u];
-            if (LW) {
-                const Real om = fma(-w, t[u], w);
-                const Real y = t[u] * S;
-                v[u] = E + y + coef[2 * Lp + k0 + u] * om;
-                S = fma(coef[3 * Lp + k0 + u], om, y);
-            } else {
-                v[u] = E;
-            }
-        }
-        const Real r = reduce8(v, lane);
-        if (rlane && k0 + ridx < nl) bacc_up[k0 + ridx] += (double)r;
-    }
+    for (int u = 0; u < kU; ++u) tp[u] = ts[(Lp - kU + u) * 32 + lane];
+    up_iter(std::true_type{}, std::false_type{}, Lp - kU);
+    for (int k0 = Lp - 2 * kU; k0 >= 0; k0 -= kU) up_iter(std::true_type{}, std::true_type{}, k0);
+    up_iter(std::false_type{}, std::true_type{}, -kU);
 }
 
 // MM = number of molecules of the table-fused path (compile-time so the prefetched table values
