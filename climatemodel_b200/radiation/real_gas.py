@@ -161,3 +161,12 @@ def dtransmission_dq(p1, p2, p_all, nu_band, delta_nu_band, nu_all, tau, absorpt
                                                    _i32p(inu), dptr(nu_band), nu_band.size, float(delta_nu_band),
                                                    dptr(k_band), dptr(scale), float(g), dptr(out)))
     return out
+
+
+def __getattr__(name):
+    # RealGas is defined in real_gas_model (which imports this module); resolve lazily so that
+    # ``from climatemodel_b200.radiation.real_gas import RealGas`` works like the reference import.
+    if name == 'RealGas':
+        from .real_gas_model import RealGas
+        return RealGas
+    raise AttributeError(name)
