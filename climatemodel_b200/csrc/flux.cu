@@ -30,16 +30,39 @@ static int ensure_tidx(cmb200_plan *p, int64_t n_col, const double *T_tau, const
     return CMB200_OK;
 }
 
-// Decide how many warps share one column and lay out the partial-sum slots.
-static int ensure_partition(cmb200_plan *p, int64_t n_col, int warps_per_cta) {
+// Relative cost of one pass of the flux kernel, used to balance the warps of a CTA: a long-wave
+// pass carries the emission recurrences, and every (part, band) run ends with a replay-only pass.
+static const double kCostLW = 1.5, kCostRun = 0.4;
+
+// Work decomposition: W warps per CTA (from the shared-memory budget), C CTAs per column (more
+// than one only when there are fewer columns than resident CTAs), parts = C * W contiguous runs
+// of segments of equal estimated cost, and one partial-sum slot per (part, band) run.
+static int ensure_partition(cmb200_plan *p, int64_t n_col, int W, int resident_ctas) {
     Partition &pt = p->partition;
-    if (pt.n_col == n_col) return CMB200_OK;
-    const int64_t target = (int64_t)sm_count(p->device) * warps_per_cta * 2;
-    int parts = 1;
-    if (n_col < target) parts = (int)std::min<int64_t>(p->n_seg, (target + n_col - 1) / n_col);
-    if (parts < 1) parts = 1;
+    if (pt.n_col == n_col && pt.warps == W) return CMB200_OK;
+    int C = 1;
+    if (n_col < resident_ctas) {
+        const int64_t want = (resident_ctas + n_col - 1) / n_col;
+        const int64_t most = std::max<int64_t>(1, p->n_seg / (2 * W));   // keep two segments per warp
+        C = (int)std::max<int64_t>(1, std::min(want, most));
+    }
+    const int parts = C * W, n_seg = p->n_seg;
+    std::vector<double> prefix(n_seg + 1, 0.0);
+    for (int s = 0; s < n_seg; ++s) {
+        const int j = p->hseg_band[s];
+        double c = p->hsw[j] ? 1.0 : kCostLW;
+        if (s == 0 || p->hseg_band[s - 1] != j) c += kCostRun * (p->hsw[j] ? 1.0 : kCostLW);
+        prefix[s + 1] = prefix[s] + c;
+    }
     std::vector<int32_t> seg0(parts + 1), slot0(parts), bslot(p->B + 1, 0);
-    for (int i = 0; i <= parts; ++i) seg0[i] = (int32_t)((int64_t)i * p->n_seg / parts);
+    for (int i = 0; i <= parts; ++i) {
+        const double want = prefix[n_seg] * i / parts;
+        int s = (int)(std::lower_bound(prefix.begin(), prefix.end(), want - 1e-9) - prefix.begin());
+        if (s > 0 && want - prefix[s - 1] < prefix[s] - want) --s;       // nearer boundary
+        seg0[i] = std::min(std::max(s, i ? seg0[i - 1] : 0), n_seg);
+    }
+    seg0[0] = 0;
+    seg0[parts] = n_seg;
     std::vector<int32_t> slot_band;
     for (int i = 0; i < parts; ++i) {
         slot0[i] = (int32_t)slot_band.size();
@@ -52,6 +75,8 @@ static int ensure_partition(cmb200_plan *p, int64_t n_col, int warps_per_cta) {
     }
     for (int j = 0; j <= p->B; ++j)
         bslot[j] = (int32_t)(std::lower_bound(slot_band.begin(), slot_band.end(), j) - slot_band.begin());
+    pt.warps = W;
+    pt.ctas_per_col = C;
     pt.parts = parts;
     pt.n_slots = (int)slot_band.size();
     CMB_CUDA(pt.part_seg0.upload(seg0.data(), seg0.size()));
@@ -64,8 +89,8 @@ static int ensure_partition(cmb200_plan *p, int64_t n_col, int warps_per_cta) {
 
 template <typename Real, int MM>
 static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *Tint, cudaStream_t s) {
-    const int L = p->L;
-    const size_t per_warp = flux_warp_smem<Real, MM>(L);
+    const int L = p->L, Lp = padded_layers(L);
+    const CtaSmem<Real, MM> lay(L);
     const double span = MM > 0 ? (double)MM * L * p->nT_pad * (double)p->pitch * sizeof(Real) / 16.0 : (double)L * (double)p->N;
     if (span >= 4294967296.0) {
         set_error("table / tau rows exceed the 32-bit row offsets of the flux kernel (%.3g units)", span);
@@ -73,17 +98,41 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     }
     int max_smem = 0;
     CMB_CUDA(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, p->device));
-    int warps = (int)std::min<size_t>(8, (size_t)max_smem / per_warp);
-    if (warps < 1) {
-        set_error("%d levels need %zu bytes of shared memory per warp; the device offers %d", L, per_warp, max_smem);
+    const int W = (size_t)max_smem > lay.shared_total
+                      ? (int)std::min<size_t>(8, ((size_t)max_smem - lay.shared_total) / lay.warp_total)
+                      : 0;
+    if (W < 1) {
+        set_error("%d levels need %zu bytes of shared memory per CTA; the device offers %d", L, lay.total(1), max_smem);
         return CMB200_ERR_LIMIT;
     }
-    int rc = ensure_partition(p, io->n_col, warps);
+    const size_t smem = lay.total(W);
+    CMB_CUDA(cudaFuncSetAttribute(flux_kernel<Real, MM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int ctas_per_sm = 1;
+    CMB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, flux_kernel<Real, MM>, W * 32, smem));
+    const int resident = sm_count(p->device) * std::max(1, ctas_per_sm);
+    int rc = ensure_partition(p, io->n_col, W, resident);
     if (rc) return rc;
     const Partition &pt = p->partition;
-    if (pt.parts > 1) {
-        size_t need = (size_t)io->n_col * pt.n_slots * 2 * L;
+    if (pt.n_slots == 0) {     // no segment in this plan's band / segment range: every sum is empty
+        const size_t n = (size_t)io->n_col;
+        if (io->up) CMB_CUDA(cudaMemsetAsync(io->up, 0, n * L * p->B * sizeof(double), s));
+        if (io->down) CMB_CUDA(cudaMemsetAsync(io->down, 0, n * L * p->B * sizeof(double), s));
+        if (io->net) CMB_CUDA(cudaMemsetAsync(io->net, 0, n * L * sizeof(double), s));
+        if (io->heating) CMB_CUDA(cudaMemsetAsync(io->heating, 0, n * (L - 1) * sizeof(double), s));
+        return CMB200_OK;
+    }
+    const int C = pt.ctas_per_col;
+    const int64_t n_tasks = io->n_col * C;
+    const int64_t grid = std::min<int64_t>(n_tasks, resident);
+    {
+        const size_t regions = C == 1 ? (size_t)grid : (size_t)io->n_col;
+        const size_t need = regions * pt.n_slots * 2 * L;
         if (p->scratch.n < need) CMB_CUDA(p->scratch.alloc(need));
+        const size_t cneed = ((size_t)grid * p->B * 4 * Lp * sizeof(Real) + 7) / 8;
+        if (p->coefbuf.n < cneed) {
+            CMB_CUDA(p->coefbuf.alloc(cneed));
+            CMB_CUDA(cudaMemsetAsync(p->coefbuf.p, 0, cneed * sizeof(double), s));   // the padding stays zero
+        }
     }
     FluxArgs<Real> a;
     memset(&a, 0, sizeof(a));
@@ -91,11 +140,14 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     a.B = p->B;
     a.M = p->M;
     a.nT_pad = p->nT_pad;
-    a.parts = pt.parts;
     a.n_slots = pt.n_slots;
+    a.band_lo = p->band_lo;
+    a.band_hi = p->band_hi;
+    a.ctas_per_col = C;
     a.N = p->N;
     a.pitch = p->pitch;
     a.n_col = io->n_col;
+    a.n_tasks = n_tasks;
     a.geo = p->geo.p;
     a.Pint = p->P.p;
     a.hdP = p->hdP.p;
@@ -111,6 +163,7 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     a.seg_c0 = p->seg_c0.p;
     a.part_seg0 = pt.part_seg0.p;
     a.part_slot0 = pt.part_slot0.p;
+    a.band_slot0 = pt.band_slot0.p;
     a.pc = PlanckConst{p->c.h_planck, p->c.speed_of_light, p->c.k_boltzmann};
     a.T_star = p->T_star;
     a.star_geom = p->R_star * p->R_star / (p->dist * p->dist);
@@ -133,20 +186,11 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     a.net = io->net;
     a.heating = io->heating;
     a.scratch = p->scratch.p;
+    a.coefbuf = (Real *)p->coefbuf.p;
 
-    const size_t smem = per_warp * warps;
-    CMB_CUDA(cudaFuncSetAttribute(flux_kernel<Real, MM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const int64_t tasks = io->n_col * pt.parts;
-    const int64_t blocks = (tasks + warps - 1) / warps;
-    if (blocks > 0x7fffffffLL) {
-        set_error("too many columns for one launch");
-        return CMB200_ERR_LIMIT;
-    }
-    if (pt.n_slots || pt.parts == 1) {
-        flux_kernel<Real, MM><<<(unsigned)blocks, warps * 32, smem, s>>>(a);
-        CMB_LAUNCHED();
-    }
-    if (pt.parts > 1) {
+    flux_kernel<Real, MM><<<(unsigned)grid, W * 32, smem, s>>>(a);
+    CMB_LAUNCHED();
+    if (C > 1) {
         flux_finalize_kernel<<<(unsigned)io->n_col, 128, L * sizeof(double), s>>>(
             L, p->B, p->band_lo, p->band_hi, pt.n_slots, io->n_col, pt.band_slot0.p, p->band_delta.p,
             p->scratch.p, p->P.p, a.g_over_cp, io->up, io->down, io->net, io->heating);

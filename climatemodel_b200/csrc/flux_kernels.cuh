@@ -5,15 +5,25 @@
 // Per-bin form (oracle/realgas_oracle.py:get_flux_per_bin): every quantity the
 // reference builds from the band-averaged transmission matrix is linear in the per-bin
 // products E(i,k) = prod_{l=i}^{k-1} t_l with t_l = exp(-dtau_l), so each (band, bin) "chain"
-// is one exp per layer plus two first-order recurrences over the layers, and the band value is
-// the trapezoid-weighted sum of the chains.
+// is one exp per layer plus two first-order recurrences over the layers (one per direction), and
+// the band value is the trapezoid-weighted sum of the chains.
 //
-// Mapping: one warp owns one (column, part) task; each lane holds one chain at a time
-// (consecutive lanes = consecutive wavenumber bins, so table / tau rows are read coalesced).
-// The downward sweep (TOA -> surface) computes t_k and parks it in shared memory
-// ts[k][lane]; the upward sweep (surface -> TOA) replays it, so each layer costs one
-// exp, not two.  Per interface the chains are summed over the warp with shuffles and added to
-// the band accumulators; bands are folded into net flux and heating rate in the epilogue.
+// Mapping: one CTA owns one column at a time (or 1/C of it when there are few columns); the
+// per-level lookup data of the column sit once in shared memory and each of the CTA's W warps
+// takes a contiguous, cost-balanced run of "segments" (32 consecutive wavenumber bins of one
+// band, one chain per lane, so table / tau rows are read coalesced).
+//
+// A warp walks its segments in *passes* over the levels that alternate direction.  Each pass
+// carries two chains at once: the FRESH chain of segment s, whose t_k = exp(-dtau_k) is computed
+// now and parked in shared memory ts[k][lane], and the REPLAY chain of segment s-1, whose t_k is
+// read back from ts (just before the slot is overwritten) to run its sweep in the other
+// direction.  So a layer costs one exp, every pass has two independent recurrences to overlap,
+// and because both chains of a pass contribute to the same band, direction and interface, their
+// values are added *before* the warp reduction -- one reduction per pass instead of two.
+//   pass n   (down):  fresh seg n   downward sweep  |  replay seg n-1 downward sweep
+//   pass n+1 (up):    fresh seg n+1 upward sweep    |  replay seg n   upward sweep      ...
+// A band run ends with a replay-only pass.  Per-(warp, band) partial sums go to a small global
+// scratch (L2 resident) and are added in a fixed order, so results do not depend on scheduling.
 #pragma once
 #include "internal.cuh"
 
@@ -21,8 +31,9 @@ namespace cmb {
 
 template <typename Real>
 struct FluxArgs {
-    int L, B, M, nT_pad, parts, n_slots;
-    int64_t N, pitch, n_col;
+    int L, B, M, nT_pad, n_slots, band_lo, band_hi;
+    int ctas_per_col;          // C: CTAs sharing one column (1 = whole column in one CTA, in-CTA finalize)
+    int64_t N, pitch, n_col, n_tasks;
     // plan-static
     const double *geo, *Pint, *hdP;
     const int32_t *band_start, *band_len;
@@ -30,7 +41,7 @@ struct FluxArgs {
     const uint8_t *band_sw;
     const Real *wchain;
     const int64_t *chain_off;
-    const int32_t *seg_band, *seg_c0, *part_seg0, *part_slot0;
+    const int32_t *seg_band, *seg_c0, *part_seg0, *part_slot0, *band_slot0;
     PlanckConst pc;
     double T_star, star_geom, g, g_over_cp;
     // per column
@@ -42,24 +53,28 @@ struct FluxArgs {
     const uint8_t *tidx;
     const double *q;
     int64_t q_mol_stride, q_col_stride;
-    double *up, *down, *net, *heating, *scratch;
+    double *up, *down, *net, *heating;
+    // work space (written and re-read inside the kernel: never const / restrict)
+    double *scratch;           // [region][n_slots][2][L] partial band sums
+    Real *coefbuf;             // [CTA][B][4][Lp] emission coefficients of the long-wave bands
 };
 
-constexpr int kU = 8;   // layers per block of the sweeps (instruction-level parallelism)
+constexpr int kU = 8;          // layers per block of a pass (instruction-level parallelism)
 
 // Per-level, warp-uniform lookup data of one molecule kept in shared memory: q/g and the offset
-// of the table row KL[m][k][tidx] (fused path) or of the tau row k (resident-tau path).  Level k
-// sits at index k + kLevShift so that the kU levels k0+1 .. k0+kU of a block start on a 16-byte
-// boundary and are read with vector loads; levels are padded beyond L-1 with q/g = 0 and a valid
-// offset so that the sweeps need no bounds checks.
+// of the table row KL[m][k][tidx] (fused path) or of the tau row k (resident-tau path).  A block
+// of kU layers k0..k0+kU-1 touches the kU+1 interfaces k0..k0+kU; a downward pass carries the
+// first and loads k0+1..k0+kU, an upward pass carries the last and loads k0..k0+kU-1.  Interface
+// k sits at index k + 3 in off_dn / qg and at k + 4 in off_up, so both offset groups start on a
+// 16-byte boundary; everything is padded beyond L-1 with q/g = 0 and a valid offset so that the
+// sweeps need no bounds checks.
 constexpr int kLevShift = 3;
 template <typename Real>
 struct LevelView {
-    const unsigned *off;   // [MR][stride]
-    const Real *qg;        // [MR][stride]
+    const unsigned *off_dn, *off_up;   // [MR][stride]
+    const Real *qg;                    // [MR][stride]
     int stride;
-    const Real *hdp;       // [Lp]   half layer thickness, 0 in the padding
-    const Real *coef;      // [4][Lp] emission coefficients of the current long-wave band
+    const Real *hdp;                   // [Lp] half layer thickness, 0 in the padding
 };
 
 // kU consecutive, 16-byte aligned shared-memory values -> registers with 128-bit loads.
@@ -75,40 +90,54 @@ __device__ __forceinline__ void lds_block(const T *p, T (&o)[kU]) {
 #pragma unroll
     for (int u = 0; u < kU; ++u) o[u] = buf.t[u];
 }
+// The same for a run that starts one element *before* a 16-byte boundary (p + 1 is aligned).
+__device__ __forceinline__ void lds_block_m1(const double *p, double (&o)[kU]) {
+    o[0] = p[0];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        const double2 v = *reinterpret_cast<const double2 *>(p + 1 + 2 * i);
+        o[1 + 2 * i] = v.x;
+        o[2 + 2 * i] = v.y;
+    }
+    o[7] = p[7];
+}
+__device__ __forceinline__ void lds_block_m1(const float *p, float (&o)[kU]) {
+    o[0] = p[0];
+    const float4 v = *reinterpret_cast<const float4 *>(p + 1);
+    o[1] = v.x, o[2] = v.y, o[3] = v.z, o[4] = v.w;
+    const float2 w = *reinterpret_cast<const float2 *>(p + 5);
+    o[5] = w.x, o[6] = w.y;
+    o[7] = p[7];
+}
 
 __host__ __device__ inline int padded_layers(int L) { return ((L - 1) + kU - 1) / kU * kU; }
 
-// Per-warp shared-memory layout (every sub-array 16-byte aligned).
+// Shared-memory layout of one CTA (every sub-array 16-byte aligned): the column's level tables
+// once, then per warp the band accumulators and the t-store.
 template <typename Real, int MM>
-struct WarpSmem {
-    size_t off_nacc, off_off, off_qg, off_hdp, off_coef, off_ts, total;
+struct CtaSmem {
+    size_t off_offdn, off_offup, off_qg, off_hdp, shared_total, warp_bacc, warp_ts, warp_total;
     int lev_stride;
-    __host__ __device__ WarpSmem(int L) {
+    __host__ __device__ CtaSmem(int L) {
         auto up16 = [](size_t x) { return (x + 15) & ~(size_t)15; };
         const int Lp = padded_layers(L), MR = MM > 0 ? MM : 1;
-        size_t b = up16((size_t)2 * (Lp + kU) * sizeof(double));          // bacc_up, bacc_dn
-        off_nacc = b;
-        b = up16(b + (size_t)2 * L * sizeof(double));                     // nacc_up, nacc_dn
-        lev_stride = Lp + 2 * kU;                                         // level k at k + kLevShift
-        off_off = b;
+        lev_stride = Lp + kU;
+        size_t b = 0;
+        off_offdn = b;
+        b = up16(b + (size_t)MR * lev_stride * sizeof(unsigned));
+        off_offup = b;
         b = up16(b + (size_t)MR * lev_stride * sizeof(unsigned));
         off_qg = b;
         b = up16(b + (size_t)MR * lev_stride * sizeof(Real));
         off_hdp = b;
         b = up16(b + (size_t)Lp * sizeof(Real));
-        off_coef = b;
-        b = up16(b + (size_t)4 * Lp * sizeof(Real));
-        off_ts = b;
-        size_t ts_bytes = (size_t)Lp * 32 * sizeof(Real);
-        size_t planck_bytes = (size_t)2 * L * sizeof(double);             // band-prologue scratch
-        b = up16(b + (ts_bytes > planck_bytes ? ts_bytes : planck_bytes));
-        total = b;
+        shared_total = b;
+        warp_bacc = 0;                                                     // bacc_up, bacc_dn [Lp + kU] each
+        warp_ts = up16((size_t)2 * (Lp + kU) * sizeof(double));
+        warp_total = up16(warp_ts + (size_t)Lp * 32 * sizeof(Real));
     }
+    __host__ __device__ size_t total(int warps) const { return shared_total + warp_total * warps; }
 };
-template <typename Real, int MM>
-__host__ __device__ inline size_t flux_warp_smem(int L) {
-    return WarpSmem<Real, MM>(L).total;
-}
 
 // exp(-x) for the layer transmissivity.  FP64: n = rint(-x log2 e), r = -x - n ln2 (two-term
 // Cody-Waite), degree-11 near-minimax polynomial on |r| <= ln2/2 (max rel. error 1.6e-17 before
@@ -203,22 +232,25 @@ __device__ __forceinline__ Real reduce8(const Real (&v)[8], int lane) {
     return c;
 }
 
-// One direction pair of sweeps for the chain held by this lane.  LW selects the long-wave
-// variant (emission recurrences); MM as in flux_kernel.
-//   down, TOA -> surface:  t_k = exp(-dtau_k);  E <- E t_k;  value at interface k+1
-//   up,   surface -> TOA:  replay t_k from shared memory;    value at interface k
-// The nu-weight w (and the boundary source) is folded into the initial state so that the values
-// handed to the warp reduction are already weighted.
+// One pass over the levels for the (up to) two chains this lane holds.
+//   UP = false: TOA -> surface, value of layer k belongs to interface k+1 (caller passes bacc_dn + 1)
+//   UP = true:  surface -> TOA, value of layer k belongs to interface k   (caller passes bacc_up)
+//   FRESH:      segment whose t_k are computed in this pass and stored to ts (weight wF, rows src_lane)
+//   replay:     segment whose t_k are read back from ts (weight wR; wR = 0 on the first pass of a band)
+//   LW:         long-wave band (emission recurrences; coefL / coefG = this direction's coefficient rows)
+// b0 is the boundary source of the direction (stellar at the top, ground at the bottom); the
+// nu-weight is folded into the initial state so that the values handed to the warp reduction are
+// already weighted.
 //
-// Both sweeps are software-pipelined by hand over blocks of kU layers, because a lane's work is
-// one long dependency chain and only ~1.5 warps per scheduler fit next to the t-store: while the
-// kU independent exp evaluations of block b are in flight (stage A), the serial recurrence of
-// block b-1 (stage B) and its warp reduction (stage C) are issued in between, statement by
-// statement -- ptxas keeps this order, so the FP64 pipe always has independent work.
-template <typename Real, int MM, bool LW>
-__device__ __forceinline__ void sweep_chain(const int lane, const int nl, const int Lp, const Real w, const Real bs,
-                                            const Real bg, const void *src_lane, const LevelView<Real> lv, Real *ts,
-                                            double *bacc_up, double *bacc_dn) {
+// The pass is software-pipelined by hand over blocks of kU layers, because a lane's work is a set
+// of long dependency chains and only two warps per scheduler fit next to the t-store: while the kU
+// independent exp evaluations of block b are in flight (stage A), the serial recurrences of block
+// b-1 (stage B, both chains) and the warp reduction of their summed values (stage C) are issued
+// in between, statement by statement -- ptxas keeps this order.
+template <typename Real, int MM, bool LW, bool UP, bool FRESH>
+__device__ __forceinline__ void sweep_pass(const int lane, const int nl, const int Lp, const Real wF, const Real wR,
+                                           const Real b0, const void *src_lane, const LevelView<Real> lv, Real *tsl,
+                                           double *bacc, const Real *coefL, const Real *coefG) {
     constexpr bool FUSED = MM > 0;
     constexpr int MR = MM > 0 ? MM : 1;
     constexpr bool F64 = sizeof(Real) == 8;
@@ -229,34 +261,10 @@ __device__ __forceinline__ void sweep_chain(const int lane, const int nl, const 
     const bool h4 = lane & 16, h3 = lane & 8, h2 = lane & 4;
     const int ridx = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
     const bool rlane = (lane & 3) == 0;
-    const Real *hdp = lv.hdp, *coef = lv.coef;
+    const int kfirst = UP ? Lp - kU : 0, kstep = UP ? -kU : kU;
 
-    // raw[u][m]: table value (or tau) of interface k0+1+u, loaded one block ahead so the L2/HBM
-    // latency hides behind the previous block's work.
-    Src raw[kU][MR];
-    auto load_block = [&](int kfirst) {      // kfirst = k0 + 1, k0 a multiple of kU
-#pragma unroll
-        for (int m = 0; m < MR; ++m) {
-            unsigned off[kU];
-            lds_block(lv.off + m * lv.stride + kfirst + kLevShift, off);
-#pragma unroll
-            for (int u = 0; u < kU; ++u) raw[u][m] = *(const Src *)(src_bytes + (size_t)off[u] * kOffUnit);
-        }
-    };
-    Src Iprev;
-    if (FUSED) {
-        Real acc = Real(0);
-#pragma unroll
-        for (int m = 0; m < MR; ++m)
-            acc += lv.qg[m * lv.stride + kLevShift] * (Real)(*(const Src *)(src_bytes + (size_t)lv.off[m * lv.stride + kLevShift] * kOffUnit));
-        Iprev = (Src)acc;
-    } else {
-        Iprev = *(const Src *)(src_bytes + (size_t)lv.off[kLevShift] * kOffUnit);
-    }
-    load_block(1);
-
-    // ---- shared pieces of the pipeline stages -----------------------------------------------------
-    Real E, H, tp[kU], v[kU], a4[4], a2[2], c1;      // recurrence state, block b-1's t and values
+    // ---- warp reduction of v[0..7], split into five steps for the interleave ----------------------
+    Real v[kU], a4[4], a2[2], c1;
     auto C1 = [&]() {
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
@@ -277,320 +285,405 @@ __device__ __forceinline__ void sweep_chain(const int lane, const int nl, const 
     };
     auto C4 = [&]() { c1 += __shfl_xor_sync(full, c1, 2); };
     auto C5 = [&]() { c1 += __shfl_xor_sync(full, c1, 1); };
-
-    // ---- downward sweep ---------------------------------------------------------------------------------
-    auto Bdn = [&](int kb, int u) {           // recurrence step of layer kb+u (block b-1)
-        E *= tp[u];
-        if (LW) {
-            const Real om = fma(-w, tp[u], w);              // w (1 - t)
-            const Real S = tp[u] * H;
-            v[u] = E + S + coef[kb + u] * om;
-            H = fma(coef[Lp + kb + u], om, S);
-        } else {
-            v[u] = E;
-        }
+    auto Cstore = [&](int kc) {
+        if (rlane && kc + ridx < nl) bacc[kc + ridx] += (double)c1;
     };
-    auto down_iter = [&](auto doA_t, auto doB_t, const int k0) {
-        constexpr bool DO_A = decltype(doA_t)::value, DO_B = decltype(doB_t)::value;
-        const int kb = k0 - kU;
-        Real x[kU], t[kU];
-        // stage A set-up: layer integrand of the block's interfaces, next block's loads, dtau
-        if (DO_A) {
-            Src In[kU];
-            if (FUSED) {
-                Real qg[kU], acc[kU];
-                lds_block(lv.qg + k0 + 1 + kLevShift, qg);
-#pragma unroll
-                for (int u = 0; u < kU; ++u) acc[u] = qg[u] * (Real)raw[u][0];
-#pragma unroll
-                for (int m = 1; m < MR; ++m) {
-                    lds_block(lv.qg + m * lv.stride + k0 + 1 + kLevShift, qg);
-#pragma unroll
-                    for (int u = 0; u < kU; ++u) acc[u] = fma(qg[u], (Real)raw[u][m], acc[u]);
-                }
-#pragma unroll
-                for (int u = 0; u < kU; ++u) In[u] = (Src)acc[u];
-            } else {
-#pragma unroll
-                for (int u = 0; u < kU; ++u) In[u] = raw[u][0];
-            }
-            if (k0 + kU < Lp) load_block(k0 + 1 + kU);
-            Real hd[kU];
-            if (FUSED) lds_block(hdp + k0, hd);
-#pragma unroll
-            for (int u = 0; u < kU; ++u) {
-                const Src lo = u ? In[u - 1] : Iprev;
-                x[u] = FUSED ? (Real)(hd[u] * (Real)(lo + In[u])) : (Real)(In[u] - lo);
-            }
-            Iprev = In[kU - 1];
+
+    // ---- recurrence step of layer kb+u for both chains (stage B) --------------------------------------
+    Real EF = wF * b0, HF = Real(0), ER = wR * b0, HR = Real(0);
+    Real tp[kU], tR[kU];
+    auto Bstep = [&](int kb, int u, Real(&out)[kU]) {
+        Real cl = Real(0), cg = Real(0), valF = Real(0), valR;
+        if (LW) {
+            cl = coefL[kb + u];
+            cg = coefG[kb + u];
         }
-        if constexpr (F64) {
-            double tn[kU], r[kU], p[kU];
-            int n[kU];
+        if constexpr (FRESH) {
+            EF *= tp[u];
+            if (LW) {
+                const Real om = fma(-wF, tp[u], wF);          // w (1 - t)
+                const Real S = tp[u] * HF;
+                valF = EF + S + cl * om;
+                HF = fma(cg, om, S);
+            } else {
+                valF = EF;
+            }
+        }
+        ER *= tR[u];
+        if (LW) {
+            const Real om = fma(-wR, tR[u], wR);
+            const Real S = tR[u] * HR;
+            valR = ER + S + cl * om;
+            HR = fma(cg, om, S);
+        } else {
+            valR = ER;
+        }
+        out[u] = FRESH ? valF + valR : valR;
+    };
+    auto ord = [](int o) { return UP ? kU - 1 - o : o; };   // order in which a block's layers are swept
+
+    if constexpr (FRESH) {
+        // raw[u][m]: table value (or tau) of the block's loaded interfaces, fetched one block ahead so
+        // that the L2 / HBM latency hides behind the previous block's work.
+        const unsigned *offs = UP ? lv.off_up : lv.off_dn;   // either way the group of block k0 starts at k0 + 4
+        Src raw[kU][MR];
+        auto ld = [&](unsigned off) { return *(const Src *)(src_bytes + (size_t)off * kOffUnit); };
+        auto load_block = [&](int k0) {
+#pragma unroll
+            for (int m = 0; m < MR; ++m) {
+                unsigned off[kU];
+                lds_block(offs + m * lv.stride + k0 + 4, off);
+#pragma unroll
+                for (int u = 0; u < kU; ++u) raw[u][m] = ld(off[u]);
+            }
+        };
+        Src Ic;                                               // the carried interface of the next block
+        {
+            const int k = (UP ? Lp : 0) + kLevShift;
+            if (FUSED) {
+                Real acc = Real(0);
+#pragma unroll
+                for (int m = 0; m < MR; ++m) acc += lv.qg[m * lv.stride + k] * (Real)ld(lv.off_dn[m * lv.stride + k]);
+                Ic = (Src)acc;
+            } else {
+                Ic = ld(lv.off_dn[k]);
+            }
+        }
+        load_block(kfirst);
+
+        auto iter = [&](auto doA_t, auto doB_t, const int k0) {
+            constexpr bool DO_A = decltype(doA_t)::value, DO_B = decltype(doB_t)::value;
+            const int kb = k0 - kstep;
+            Real x[kU], t[kU];
+            // stage A set-up: layer integrand at the block's interfaces, next block's loads, dtau
             if (DO_A) {
+                Src In[kU];
+                if (FUSED) {
+                    Real qg[kU], acc[kU];
+#pragma unroll
+                    for (int m = 0; m < MR; ++m) {
+                        if (UP)
+                            lds_block_m1(lv.qg + m * lv.stride + k0 + kLevShift, qg);
+                        else
+                            lds_block(lv.qg + m * lv.stride + k0 + 1 + kLevShift, qg);
+#pragma unroll
+                        for (int u = 0; u < kU; ++u) acc[u] = m ? fma(qg[u], (Real)raw[u][m], acc[u]) : qg[u] * (Real)raw[u][0];
+                    }
+#pragma unroll
+                    for (int u = 0; u < kU; ++u) In[u] = (Src)acc[u];
+                } else {
+#pragma unroll
+                    for (int u = 0; u < kU; ++u) In[u] = raw[u][0];
+                }
+                if (UP ? k0 >= kU : k0 + kU < Lp) load_block(k0 + kstep);
+                Real hd[kU];
+                if (FUSED) lds_block(lv.hdp + k0, hd);
 #pragma unroll
                 for (int u = 0; u < kU; ++u) {
-                    x[u] = clamp_thickness(x[u]);
-                    tn[u] = fma(-x[u], kExpC[11], kExpC[12]);
+                    const Src lo = UP ? In[u] : (u ? In[u - 1] : Ic);
+                    const Src hi = UP ? (u < kU - 1 ? In[u + 1] : Ic) : In[u];
+                    x[u] = FUSED ? (Real)(hd[u] * (Real)(lo + hi)) : (Real)(hi - lo);
                 }
+                Ic = UP ? In[0] : In[kU - 1];
             }
-            if (DO_B) { Bdn(kb, 0); Bdn(kb, 1); }
-            if (DO_A) {
-#pragma unroll
-                for (int u = 0; u < kU; ++u) {
-                    n[u] = __double2loint(tn[u]);
-                    tn[u] -= kExpC[12];
-                }
-            }
-            if (DO_B) { Bdn(kb, 2); Bdn(kb, 3); }
-            if (DO_A) {
-#pragma unroll
-                for (int u = 0; u < kU; ++u) r[u] = fma(tn[u], kExpC[13], -x[u]);
-            }
-            if (DO_B) { Bdn(kb, 4); Bdn(kb, 5); }
-            if (DO_A) {
-#pragma unroll
-                for (int u = 0; u < kU; ++u) {
-                    r[u] = fma(tn[u], kExpC[14], r[u]);
-                    p[u] = kExpC[0];
-                }
-            }
-            if (DO_B) { Bdn(kb, 6); Bdn(kb, 7); }
-#pragma unroll
-            for (int i = 1; i <= 10; ++i) {
+            if constexpr (F64) {
+                double tn[kU], r[kU], p[kU];
+                int n[kU];
                 if (DO_A) {
 #pragma unroll
-                    for (int u = 0; u < kU; ++u) p[u] = fma(p[u], r[u], kExpC[i]);
+                    for (int u = 0; u < kU; ++u) {
+                        x[u] = clamp_thickness(x[u]);
+                        tn[u] = fma(-x[u], kExpC[11], kExpC[12]);
+                    }
+                }
+                if (DO_B) { Bstep(kb, ord(0), v); Bstep(kb, ord(1), v); }
+                if (DO_A) {
+#pragma unroll
+                    for (int u = 0; u < kU; ++u) {
+                        n[u] = __double2loint(tn[u]);
+                        tn[u] -= kExpC[12];
+                    }
+                }
+                if (DO_B) { Bstep(kb, ord(2), v); Bstep(kb, ord(3), v); }
+                if (DO_A) {
+#pragma unroll
+                    for (int u = 0; u < kU; ++u) r[u] = fma(tn[u], kExpC[13], -x[u]);
+                }
+                if (DO_B) { Bstep(kb, ord(4), v); Bstep(kb, ord(5), v); }
+                if (DO_A) {
+#pragma unroll
+                    for (int u = 0; u < kU; ++u) {
+                        r[u] = fma(tn[u], kExpC[14], r[u]);
+                        p[u] = kExpC[0];
+                    }
+                }
+                if (DO_B) { Bstep(kb, ord(6), v); Bstep(kb, ord(7), v); }
+#pragma unroll
+                for (int i = 1; i <= 10; ++i) {
+                    if (DO_A) {
+#pragma unroll
+                        for (int u = 0; u < kU; ++u) p[u] = fma(p[u], r[u], kExpC[i]);
+                    }
+                    if (DO_B) {
+                        if (i == 1) C1();
+                        if (i == 3) C2();
+                        if (i == 5) C3();
+                        if (i == 7) C4();
+                        if (i == 9) C5();
+                    }
+                }
+                if (DO_A) {
+#pragma unroll
+                    for (int u = 0; u < kU; ++u) {
+                        p[u] = fma(p[u], r[u], kExpC[10]);
+                        t[u] = __hiloint2double(__double2hiint(p[u]) + (n[u] << 20), __double2loint(p[u]));
+                    }
+                }
+            } else {
+                if (DO_A) {
+#pragma unroll
+                    for (int u = 0; u < kU; ++u) t[u] = exp_neg(x[u]);
                 }
                 if (DO_B) {
-                    if (i == 1) C1();
-                    if (i == 3) C2();
-                    if (i == 5) C3();
-                    if (i == 7) C4();
-                    if (i == 9) C5();
+#pragma unroll
+                    for (int o = 0; o < kU; ++o) Bstep(kb, ord(o), v);
+                    C1(); C2(); C3(); C4(); C5();
                 }
             }
-            if (DO_A) {
+            if (DO_B) Cstore(kb);
+            if (DO_A) {   // swap the block's t-store rows: out comes the replay chain's t, in goes the fresh one
 #pragma unroll
                 for (int u = 0; u < kU; ++u) {
-                    p[u] = fma(p[u], r[u], kExpC[10]);
-                    t[u] = __hiloint2double(__double2hiint(p[u]) + (n[u] << 20), __double2loint(p[u]));
+                    Real *slot = tsl + (k0 + u) * 32;
+                    tR[u] = *slot;
+                    *slot = t[u];
+                    tp[u] = t[u];
                 }
             }
+        };
+        iter(std::true_type{}, std::false_type{}, kfirst);
+        if (UP) {
+            for (int k0 = Lp - 2 * kU; k0 >= 0; k0 -= kU) iter(std::true_type{}, std::true_type{}, k0);
+            iter(std::false_type{}, std::true_type{}, -kU);
         } else {
-            if (DO_A) {
+            for (int k0 = kU; k0 < Lp; k0 += kU) iter(std::true_type{}, std::true_type{}, k0);
+            iter(std::false_type{}, std::true_type{}, Lp);
+        }
+    } else {
+        // ---- replay only: recurrence of block b interleaved with the reduction of the block before --
+        Real tn8[kU], vp[kU];
+        auto iter = [&](auto doB_t, auto doC_t, const int k0) {
+            constexpr bool DO_B = decltype(doB_t)::value, DO_C = decltype(doC_t)::value;
+            if (DO_B && (UP ? k0 >= kU : k0 + kU < Lp)) {
 #pragma unroll
-                for (int u = 0; u < kU; ++u) t[u] = exp_neg(x[u]);
+                for (int u = 0; u < kU; ++u) tn8[u] = tsl[(k0 + kstep + u) * 32];
+            }
+            if (DO_B) Bstep(k0, ord(0), vp);
+            if (DO_C) C1();
+            if (DO_B) { Bstep(k0, ord(1), vp); Bstep(k0, ord(2), vp); }
+            if (DO_C) C2();
+            if (DO_B) { Bstep(k0, ord(3), vp); Bstep(k0, ord(4), vp); }
+            if (DO_C) C3();
+            if (DO_B) Bstep(k0, ord(5), vp);
+            if (DO_C) C4();
+            if (DO_B) { Bstep(k0, ord(6), vp); Bstep(k0, ord(7), vp); }
+            if (DO_C) {
+                C5();
+                Cstore(k0 - kstep);
             }
             if (DO_B) {
 #pragma unroll
-                for (int u = 0; u < kU; ++u) Bdn(kb, u);
-                C1(); C2(); C3(); C4(); C5();
+                for (int u = 0; u < kU; ++u) {
+                    v[u] = vp[u];
+                    tR[u] = tn8[u];
+                }
             }
-        }
-        if (DO_B) {
-            if (rlane && kb + ridx < nl) bacc_dn[kb + ridx + 1] += (double)c1;
-        }
-        if (DO_A) {
+        };
 #pragma unroll
-            for (int u = 0; u < kU; ++u) {
-                ts[(k0 + u) * 32 + lane] = t[u];
-                tp[u] = t[u];
-            }
-        }
-    };
-    E = w * bs;
-    H = Real(0);
-    down_iter(std::true_type{}, std::false_type{}, 0);
-    for (int k0 = kU; k0 < Lp; k0 += kU) down_iter(std::true_type{}, std::true_type{}, k0);
-    down_iter(std::false_type{}, std::true_type{}, Lp);
-
-    // ---- upward sweep: recurrence of block b interleaved with the reduction of block b+1 ------------
-    Real S = Real(0), tn8[kU], vp[kU];
-    auto Bup = [&](int kb, int u) {
-        E *= tp[u];
-        if (LW) {
-            const Real om = fma(-w, tp[u], w);
-            const Real y = tp[u] * S;
-            vp[u] = E + y + coef[2 * Lp + kb + u] * om;
-            S = fma(coef[3 * Lp + kb + u], om, y);
+        for (int u = 0; u < kU; ++u) tR[u] = tsl[(kfirst + u) * 32];
+        iter(std::true_type{}, std::false_type{}, kfirst);
+        if (UP) {
+            for (int k0 = Lp - 2 * kU; k0 >= 0; k0 -= kU) iter(std::true_type{}, std::true_type{}, k0);
+            iter(std::false_type{}, std::true_type{}, -kU);
         } else {
-            vp[u] = E;
+            for (int k0 = kU; k0 < Lp; k0 += kU) iter(std::true_type{}, std::true_type{}, k0);
+            iter(std::false_type{}, std::true_type{}, Lp);
         }
-    };
-    auto up_iter = [&](auto doB_t, auto doC_t, const int k0) {
-        constexpr bool DO_B = decltype(doB_t)::value, DO_C = decltype(doC_t)::value;
-        // prefetch t of the block after this one (k0 - kU) while this block's chain runs
-        if (DO_B && k0 >= kU) {
-#pragma unroll
-            for (int u = 0; u < kU; ++u) tn8[u] = ts[(k0 - kU + u) * 32 + lane];
-        }
-        if (DO_B) Bup(k0, 7);
-        if (DO_C) C1();
-        if (DO_B) { Bup(k0, 6); Bup(k0, 5); }
-        if (DO_C) C2();
-        if (DO_B) { Bup(k0, 4); Bup(k0, 3); }
-        if (DO_C) C3();
-        if (DO_B) Bup(k0, 2);
-        if (DO_C) C4();
-        if (DO_B) { Bup(k0, 1); Bup(k0, 0); }
-        if (DO_C) {
-            C5();
-            const int kc = k0 + kU;
-            if (rlane && kc + ridx < nl) bacc_up[kc + ridx] += (double)c1;
-        }
-        if (DO_B) {
-#pragma unroll
-            for (int u = 0; u < kU; ++u) {
-                v[u] = vp[u];
-                tp[u] = tn8[u];
-            }
-        }
-    };
-    E = w * bg;
-#pragma unroll
-    for (int u = 0; u < kU; ++u) tp[u] = ts[(Lp - kU + u) * 32 + lane];
-    up_iter(std::true_type{}, std::false_type{}, Lp - kU);
-    for (int k0 = Lp - 2 * kU; k0 >= 0; k0 -= kU) up_iter(std::true_type{}, std::true_type{}, k0);
-    up_iter(std::false_type{}, std::true_type{}, -kU);
+    }
+}
+
+template <typename Real, int MM, bool FRESH>
+__device__ __forceinline__ void dispatch_pass(const bool lw, const bool up, const int lane, const int nl, const int Lp,
+                                              const Real wF, const Real wR, const Real bs, const Real bg,
+                                              const void *src_lane, const LevelView<Real> &lv, Real *tsl,
+                                              double *bacc_up, double *bacc_dn, const Real *coef) {
+    // coefficient rows of a band: [0] dn_last, [1] dn_gen, [2] up_first, [3] up_gen
+    if (lw) {
+        if (up)
+            sweep_pass<Real, MM, true, true, FRESH>(lane, nl, Lp, wF, wR, bg, src_lane, lv, tsl, bacc_up, coef + 2 * Lp, coef + 3 * Lp);
+        else
+            sweep_pass<Real, MM, true, false, FRESH>(lane, nl, Lp, wF, wR, bs, src_lane, lv, tsl, bacc_dn + 1, coef, coef + Lp);
+    } else {
+        if (up)
+            sweep_pass<Real, MM, false, true, FRESH>(lane, nl, Lp, wF, wR, bg, src_lane, lv, tsl, bacc_up, coef, coef);
+        else
+            sweep_pass<Real, MM, false, false, FRESH>(lane, nl, Lp, wF, wR, bs, src_lane, lv, tsl, bacc_dn + 1, coef, coef);
+    }
 }
 
 // MM = number of molecules of the table-fused path (compile-time so the prefetched table values
-// live in registers); MM = 0 selects the resident-tau path.
+// live in registers); MM = 0 selects the resident-tau path.  Persistent CTAs: task = (column, c)
+// with c < ctas_per_col; warp w of the CTA sweeps part c * W + w of the column.
 template <typename Real, int MM>
 __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr bool FUSED = MM > 0;
     constexpr int MR = MM > 0 ? MM : 1;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int L = a.L, nl = a.L - 1, Lp = padded_layers(a.L), LS = Lp + kU;
-    const int64_t task = (int64_t)blockIdx.x * (blockDim.x >> 5) + warp;
-    if (task >= a.n_col * a.parts) return;
-    const int64_t col = task / a.parts;
-    const int part = (int)(task % a.parts);
+    const int tid = threadIdx.x, nthr = blockDim.x, W = nthr >> 5, warp = tid >> 5, lane = tid & 31;
+    const int L = a.L, nl = a.L - 1, Lp = padded_layers(a.L), LS = Lp + kU, C = a.ctas_per_col;
 
-    const WarpSmem<Real, MM> lay(L);
-    unsigned char *base = smem_raw + (size_t)warp * lay.total;
-    double *bacc_up = (double *)base;
-    double *bacc_dn = bacc_up + LS;
-    double *nacc_up = (double *)(base + lay.off_nacc);
-    double *nacc_dn = nacc_up + L;
-    unsigned *lev_off = (unsigned *)(base + lay.off_off);
-    Real *lev_qg = (Real *)(base + lay.off_qg);
+    const CtaSmem<Real, MM> lay(L);
+    unsigned *lev_offdn = (unsigned *)(smem_raw + lay.off_offdn);
+    unsigned *lev_offup = (unsigned *)(smem_raw + lay.off_offup);
+    Real *lev_qg = (Real *)(smem_raw + lay.off_qg);
+    Real *hdp = (Real *)(smem_raw + lay.off_hdp);
     const int lstride = lay.lev_stride;
-    Real *hdp = (Real *)(base + lay.off_hdp);
-    Real *coef = (Real *)(base + lay.off_coef);
-    Real *ts = (Real *)(base + lay.off_ts);
+    unsigned char *wbase = smem_raw + lay.shared_total + (size_t)warp * lay.warp_total;
+    double *bacc_up = (double *)(wbase + lay.warp_bacc);
+    double *bacc_dn = bacc_up + LS;
+    Real *ts = (Real *)(wbase + lay.warp_ts);
+    double *sacc = (double *)(smem_raw + lay.shared_total + lay.warp_bacc);   // warp 0's accumulators, free in the epilogue
+    Real *coef_cta = a.coefbuf + (size_t)blockIdx.x * a.B * 4 * Lp;
+    const LevelView<Real> lv{lev_offdn, lev_offup, lev_qg, lstride, hdp};
 
-    const double Tg = a.T_g[col];
-    const double albedo = a.albedo ? a.albedo[col] : a.albedo_scalar;
-    const double solar = a.star_geom * (1.0 - albedo) / 4.0;  // (R*/d)^2 (1-albedo)/4, :640-642
-
+    for (int k = tid; k < Lp; k += nthr) hdp[k] = k < nl ? (Real)a.hdP[k] : Real(0);
     for (int i = lane; i < 2 * LS; i += 32) bacc_up[i] = 0.0;
-    for (int i = lane; i < 2 * L; i += 32) nacc_up[i] = 0.0;
-    for (int i = lane; i < 4 * Lp; i += 32) coef[i] = Real(0);
-    for (int k = lane; k < Lp; k += 32) hdp[k] = k < nl ? (Real)a.hdP[k] : Real(0);
-    for (int idx = lane; idx < MR * lstride; idx += 32) {
-        const int m = idx / lstride, k = idx - m * lstride - kLevShift, kc = min(max(k, 0), L - 1);
-        if (FUSED) {
-            const int t = a.tidx[((int64_t)m * a.n_col + col) * L + kc];
-            lev_off[idx] = (unsigned)(((((int64_t)m * L + kc) * a.nT_pad + t) * a.pitch * sizeof(Real)) >> 4);
-            lev_qg[idx] = (k >= 0 && k < L) ? (Real)(a.q[m * a.q_mol_stride + col * a.q_col_stride + k] / a.g) : Real(0);
-        } else {
-            lev_off[idx] = (unsigned)((int64_t)kc * a.N);
-            lev_qg[idx] = Real(0);
-        }
-    }
-    const LevelView<Real> lv{lev_off, lev_qg, lstride, hdp, coef};
-    const double *tau_col = FUSED ? nullptr : a.tau + (int64_t)(a.tau_id ? a.tau_id[col] : 0) * L * a.N;
-    __syncwarp();
+    for (int i = lane; i < Lp * 32; i += 32) ts[i] = Real(0);   // the first replay of a run reads it with weight 0
 
-    const int s0 = a.part_seg0[part], s1 = a.part_seg0[part + 1];
-    int slot = a.parts > 1 ? a.part_slot0[part] - 1 : 0;
-    int cur = -1;
-    bool lw = false;
-    Real bg = 0, bs = 0;
+    for (int64_t task = blockIdx.x; task < a.n_tasks; task += gridDim.x) {
+        const int64_t col = task / C;
+        const int cpart = (int)(task - col * C);
+        const int64_t region = C == 1 ? (int64_t)blockIdx.x : col;
+        __syncthreads();   // the previous task is done with the tables, the scratch and sacc
 
-    auto flush = [&](int j) {
-        __syncwarp();
-        if (a.parts == 1) {
-            const double dj = a.band_delta[j];
-            for (int i = lane; i < L; i += 32) {
-                double u = bacc_up[i], d = bacc_dn[i];
-                if (a.up) a.up[(col * L + i) * a.B + j] = u;
-                if (a.down) a.down[(col * L + i) * a.B + j] = d;
-                nacc_up[i] += u * dj;
-                nacc_dn[i] += d * dj;
+        // ---- the column's level tables ---------------------------------------------------------------
+        for (int idx = tid; idx < MR * lstride; idx += nthr) {
+            const int m = idx / lstride, pos = idx - m * lstride;
+            const int k = pos - kLevShift, kc = min(max(k, 0), L - 1), kcu = min(max(k - 1, 0), L - 1);
+            if (FUSED) {
+                const uint8_t *tcol = a.tidx + ((int64_t)m * a.n_col + col) * L;
+                lev_offdn[idx] = (unsigned)(((((int64_t)m * L + kc) * a.nT_pad + tcol[kc]) * a.pitch * sizeof(Real)) >> 4);
+                lev_offup[idx] = (unsigned)(((((int64_t)m * L + kcu) * a.nT_pad + tcol[kcu]) * a.pitch * sizeof(Real)) >> 4);
+                lev_qg[idx] = (k >= 0 && k < L) ? (Real)(a.q[m * a.q_mol_stride + col * a.q_col_stride + k] / a.g) : Real(0);
+            } else {
+                lev_offdn[idx] = (unsigned)((int64_t)kc * a.N);
+                lev_offup[idx] = (unsigned)((int64_t)kcu * a.N);
+                lev_qg[idx] = Real(0);
             }
-        } else {
-            ++slot;
-            double *o = a.scratch + ((col * a.n_slots + slot) * 2) * (int64_t)L;
+        }
+
+        // ---- emission coefficients of the long-wave bands this CTA touches (real_gas.py:634-638) -----
+        const int sA = a.part_seg0[cpart * W], sB = a.part_seg0[(cpart + 1) * W];
+        const double Tg = a.T_g[col];
+        if (sA < sB) {
+            const int jA = a.seg_band[sA], jB = a.seg_band[sB - 1];
+            const int nch = (nl + 30) / 31;                       // 31 layers per warp: lane 31 only feeds B(k+1)
+            for (int wt = warp; wt < (jB - jA + 1) * nch; wt += W) {
+                const int j = jA + wt / nch, k = (wt % nch) * 31 + lane;
+                if (a.band_sw[j]) continue;
+                const double c = a.band_centre[j];
+                double bi = 0.0, bc = 0.0;
+                if (k < L) bi = M_PI * planck_wavenumber(a.pc, c, k == L - 1 ? Tg : a.Tint[col * L + k]);      // :636
+                if (k < nl) bc = M_PI * planck_wavenumber(a.pc, c, a.T[col * nl + k]);
+                const double bi1 = __shfl_down_sync(0xffffffffu, bi, 1);
+                if (lane < 31 && k < nl) {
+                    const double *g0 = a.geo + k;
+                    Real *cf = coef_cta + (size_t)j * 4 * Lp + k;
+                    cf[0] = (Real)(g0[0] * bi + g0[nl] * bc + g0[2 * nl] * bi1);                 // dn_last
+                    cf[Lp] = (Real)(g0[3 * nl] * bi + g0[4 * nl] * bc);                          // dn_gen
+                    cf[2 * Lp] = (Real)(g0[5 * nl] * bi + g0[6 * nl] * bc + g0[7 * nl] * bi1);   // up_first
+                    cf[3 * Lp] = (Real)(g0[8 * nl] * bc + g0[9 * nl] * bi1);                     // up_gen
+                }
+            }
+        }
+        __syncthreads();
+
+        // ---- this warp's run of segments -------------------------------------------------------------
+        const double albedo = a.albedo ? a.albedo[col] : a.albedo_scalar;
+        const double solar = a.star_geom * (1.0 - albedo) / 4.0;  // (R*/d)^2 (1-albedo)/4, :640-642
+        const double *tau_col = FUSED ? nullptr : a.tau + (int64_t)(a.tau_id ? a.tau_id[col] : 0) * L * a.N;
+        const int part = cpart * W + warp;
+        int s = a.part_seg0[part];
+        const int s1 = a.part_seg0[part + 1];
+        int slot = a.part_slot0[part];
+        bool up = false;
+        while (s < s1) {
+            const int j = a.seg_band[s];
+            int e = s + 1;
+            while (e < s1 && a.seg_band[e] == j) ++e;
+            const double c = a.band_centre[j];
+            const bool lw = !a.band_sw[j];
+            const Real bg = (Real)(M_PI * planck_wavenumber(a.pc, c, Tg));                   // :638
+            const Real bs = (Real)(M_PI * planck_wavenumber(a.pc, c, a.T_star) * solar);     // :640-642
+            const Real *coef = coef_cta + (size_t)j * 4 * Lp;
+            if (a.seg_c0[s] == 0 && lane == 0) {   // boundary terms: Trans(i,i) = sum of the nu-weights
+                bacc_up[L - 1] += (double)bg * a.band_sumw[j];
+                bacc_dn[0] += (double)bs * a.band_sumw[j];
+            }
+            Real wR = Real(0);
+            for (; s < e; ++s) {                   // one chain (wavenumber bin of band j) per lane
+                const int ci = a.seg_c0[s] + lane;
+                const bool act = ci < a.band_len[j];
+                const Real wF = act ? a.wchain[a.chain_off[j] + ci] : Real(0);
+                const int64_t n = a.band_start[j] + (act ? ci : 0);
+                const void *src_lane = FUSED ? (const void *)(a.KL + n) : (const void *)(tau_col + n);
+                dispatch_pass<Real, MM, true>(lw, up, lane, nl, Lp, wF, wR, bs, bg, src_lane, lv, ts + lane, bacc_up, bacc_dn, coef);
+                wR = wF;
+                up = !up;
+            }
+            dispatch_pass<Real, MM, false>(lw, up, lane, nl, Lp, Real(0), wR, bs, bg, nullptr, lv, ts + lane, bacc_up, bacc_dn, coef);
+            up = !up;
+            // ---- partial band sums of this (warp, band) run -> scratch slot ---------------------------
+            __syncwarp();
+            double *o = a.scratch + ((region * a.n_slots + slot) * 2) * (int64_t)L;
             for (int i = lane; i < L; i += 32) {
                 o[i] = bacc_up[i];
                 o[L + i] = bacc_dn[i];
             }
+            ++slot;
+            __syncwarp();
+            for (int i = lane; i < 2 * LS; i += 32) bacc_up[i] = 0.0;
+            __syncwarp();
         }
-        __syncwarp();
-        for (int i = lane; i < 2 * LS; i += 32) bacc_up[i] = 0.0;
-        __syncwarp();
-    };
+        if (C != 1) continue;      // several CTAs per column: flux_finalize_kernel adds the slots up
 
-    for (int s = s0; s < s1; ++s) {
-        const int j = a.seg_band[s];
-        const int c0 = a.seg_c0[s];
-        if (j != cur) {
-            if (cur >= 0) flush(cur);
-            cur = j;
-            // ---- band prologue: Planck sources and the pressure-quadrature coefficients ----
-            const double c = a.band_centre[j];
-            lw = !a.band_sw[j];
-            bg = (Real)(M_PI * planck_wavenumber(a.pc, c, Tg));                   // :638
-            bs = (Real)(M_PI * planck_wavenumber(a.pc, c, a.T_star) * solar);     // :640-642
-            if (lw) {
-                double *sbi = (double *)ts, *sbc = sbi + L;
-                for (int k = lane; k < L; k += 32) {
-                    double Tk = (k == L - 1) ? Tg : a.Tint[col * L + k];          // :636
-                    sbi[k] = M_PI * planck_wavenumber(a.pc, c, Tk);
-                    if (k < nl) sbc[k] = M_PI * planck_wavenumber(a.pc, c, a.T[col * nl + k]);
-                }
-                __syncwarp();
-                for (int k = lane; k < nl; k += 32) {
-                    const double bi0 = sbi[k], bi1 = sbi[k + 1], bc = sbc[k];
-                    const double *g0 = a.geo + k;
-                    coef[k] = (Real)(g0[0] * bi0 + g0[nl] * bc + g0[2 * nl] * bi1);                 // dn_last
-                    coef[Lp + k] = (Real)(g0[3 * nl] * bi0 + g0[4 * nl] * bc);                      // dn_gen
-                    coef[2 * Lp + k] = (Real)(g0[5 * nl] * bi0 + g0[6 * nl] * bc + g0[7 * nl] * bi1);   // up_first
-                    coef[3 * Lp + k] = (Real)(g0[8 * nl] * bc + g0[9 * nl] * bi1);                  // up_gen
-                }
-                __syncwarp();
+        // ---- column epilogue: band sums, net flux (:712-713), heating rate (base.py:166-168) ----------
+        __syncthreads();
+        const double *sc = a.scratch + region * a.n_slots * 2 * (int64_t)L;
+        for (int idx = tid; idx < 2 * L; idx += nthr) {
+            const int half = idx >= L, i = idx - half * L;
+            double *out = half ? a.down : a.up;
+            double acc = 0.0;
+            for (int j = a.band_lo; j < a.band_hi; ++j) {
+                double sum = 0.0;
+                const int q0 = a.band_slot0[j], q1 = a.band_slot0[j + 1];
+                for (int q = q0; q < q1; ++q) sum += sc[(q * 2 + half) * (int64_t)L + i];
+                if (out) out[(col * L + i) * a.B + j] = sum;
+                acc += sum * a.band_delta[j];
+            }
+            sacc[idx] = acc;
+        }
+        __syncthreads();
+        for (int i = tid; i < L; i += nthr) {
+            const double net = sacc[i] - sacc[L + i];
+            if (a.net) a.net[col * L + i] = net;
+            if (a.heating && i < nl) {
+                const double n1 = sacc[i + 1] - sacc[L + i + 1];
+                a.heating[col * nl + i] = a.g_over_cp * (n1 - net) / (a.Pint[i + 1] - a.Pint[i]);
             }
         }
-        // ---- this segment's chain (one wavenumber bin of band j per lane) ----------------------
-        const int ci = c0 + lane;
-        const bool act = ci < a.band_len[j];
-        const Real w = act ? a.wchain[a.chain_off[j] + ci] : Real(0);
-        const int64_t n = a.band_start[j] + (act ? ci : 0);
-        if (c0 == 0 && lane == 0) {   // boundary terms: Trans(i,i) = sum of the nu-weights
-            bacc_up[L - 1] += (double)bg * a.band_sumw[j];
-            bacc_dn[0] += (double)bs * a.band_sumw[j];
-        }
-        const void *src_lane = FUSED ? (const void *)(a.KL + n) : (const void *)(tau_col + n);
-        if (lw)
-            sweep_chain<Real, MM, true>(lane, nl, Lp, w, bs, bg, src_lane, lv, ts, bacc_up, bacc_dn);
-        else
-            sweep_chain<Real, MM, false>(lane, nl, Lp, w, bs, bg, src_lane, lv, ts, bacc_up, bacc_dn);
-    }
-    if (cur >= 0) flush(cur);
-
-    // ---- column epilogue: net flux (:712-713) and heating rate (base.py:166-168) -----------------
-    if (a.parts == 1) {
-        if (a.net)
-            for (int i = lane; i < L; i += 32) a.net[col * L + i] = nacc_up[i] - nacc_dn[i];
-        if (a.heating)
-            for (int k = lane; k < nl; k += 32) {
-                double n1 = nacc_up[k + 1] - nacc_dn[k + 1], n0 = nacc_up[k] - nacc_dn[k];
-                a.heating[col * nl + k] = a.g_over_cp * (n1 - n0) / (a.Pint[k + 1] - a.Pint[k]);
-            }
+        __syncthreads();
+        for (int idx = tid; idx < 2 * L; idx += nthr) sacc[idx] = 0.0;
     }
 }
 

@@ -17,8 +17,10 @@ int launch_nearest(const double *d_values, int64_t n, const double *d_axis, int 
 // Work decomposition of one flux evaluation, cached per (n_col) on the plan.
 struct Partition {
     int64_t n_col = -1;
-    int parts = 0;       // warps per column
-    int n_slots = 0;     // partial-sum slots per column (parts > 1 only)
+    int warps = 0;          // W: warps per CTA
+    int ctas_per_col = 1;   // C: CTAs sharing a column
+    int parts = 0;          // C * W contiguous, cost-balanced runs of segments per column
+    int n_slots = 0;        // partial-sum slots per column: one per (part, band) run
     DevBuf<int32_t> part_seg0, part_slot0, band_slot0;
 };
 
@@ -49,7 +51,7 @@ struct cmb200_plan {
     int64_t n_chains = 0;
     // device: segments (runs of 32*kChains bins inside one band) for bands [band_lo, band_hi)
     cmb::DevBuf<int32_t> seg_band, seg_c0;
-    std::vector<int32_t> hseg_band;
+    std::vector<int32_t> hseg_band, hseg_c0;
     int n_seg = 0;
     // device: level table KL[M][L][nT_pad][pitch]
     int M = 0, nT_pad = 0;
@@ -59,7 +61,7 @@ struct cmb200_plan {
     cmb::DevBuf<float> KL32;
     cmb::Partition partition;
     // per-call scratch kept between calls (grown on demand)
-    cmb::DevBuf<double> Tint, scratch;
+    cmb::DevBuf<double> Tint, scratch, coefbuf;
     cmb::DevBuf<uint8_t> tidx;
 };
 

@@ -154,6 +154,7 @@ int build_segments(cmb200_plan *p) {
     p->n_seg_total = g;
     p->n_seg = (int)sb.size();
     p->hseg_band = sb;
+    p->hseg_c0 = sc;
     CMB_CUDA(p->seg_band.upload(sb.data(), sb.size()));
     CMB_CUDA(p->seg_c0.upload(sc.data(), sc.size()));
     CMB_CUDA(cudaDeviceSynchronize());

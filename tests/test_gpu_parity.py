@@ -217,19 +217,21 @@ def test_batched_fused_columns_against_oracle(name, n_col):
 
 
 def test_whole_column_mode_equals_split_mode():
-    """Few columns are split over many warps (partial sums + finalize kernel); many columns run
-    one warp per column with the epilogue fused.  Same column, both ways."""
+    """Few columns are split over several CTAs (partial sums + finalize kernel); many columns run
+    one CTA per column with the epilogue fused.  Same column, both ways: the band sums are added in
+    a different order, so fluxes agree to rounding and the heating rate (a difference of net
+    fluxes) to rounding relative to the fluxes."""
     c = load_case('two_mol_nz41')
     plan = make_plan(c, tables=True)
     T, T_g, T_tau, albedo, q = batch_inputs(c, 3, seed=5)
     few = plan.flux(T, T_g, T_tau=T_tau, q=q, albedo=albedo)
-    n_rep = 1200                                     # > 148 SMs x warps x 2 -> whole-column mode
+    n_rep = 1200                                     # > resident CTAs -> one CTA per column
     rep = lambda a: np.ascontiguousarray(np.tile(a, (n_rep,) + (1,) * (a.ndim - 1)))
     many = plan.flux(rep(T), rep(T_g), T_tau=rep(T_tau), albedo=rep(albedo),
                      q=np.ascontiguousarray(np.tile(q, (1, n_rep, 1))))
     for k in ('up', 'down', 'net', 'heating'):
-        assert relmax(many[k][:3], few[k]) < 1e-13
-        assert np.array_equal(many[k][:3], many[k][-3:])         # deterministic across warps
+        assert relmax(many[k][:3], few[k]) < (1e-10 if k == 'heating' else 1e-13)
+        assert np.array_equal(many[k][:3], many[k][-3:])         # deterministic across CTAs
 
 
 def test_tau_id_selects_table():

@@ -94,19 +94,21 @@ def test_olr_breakdown_adds_up(mods):
 def test_assigning_tau_and_q_args_like_the_notebooks(mods):
     """centa_presentation/base.py:38-50 recomputes tau after changing q_funcs_args and assigns it."""
     rg, hum, tp = mods
-    gas = build(mods, 'co2_nz100_iso')
+    gas = build(mods, 'co2_nz50_earth')           # temperature falls with height: more CO2, less OLR
     before = gas.get_flux()[0][0].copy()
     gas.q_funcs_args = {'CO2_no_sw': (740, 80000)}
     gas.tau_interface = rg.optical_depth(gas.p_interface[:, 0], np.ones(gas.nz) * gas.T_g, gas.nu,
                                          gas.molecule_names, gas.q_funcs, gas.q_funcs_args)
     after = gas.get_flux()[0][0]
     delta = gas.nu_bands['delta']
-    assert np.sum(after * delta) < np.sum(before * delta)          # doubling CO2 lowers the OLR
+    assert np.sum(after * delta) < np.sum(before * delta) - 1.0    # doubling CO2 lowers the OLR (W/m^2)
 
 
 def test_auto_Tg_guess_balances_the_column(mods):
     rg, hum, tp = mods
     gas = quiet(rg.RealGas, nz=30, ny=1, molecule_names=['CO2_no_sw'], q_funcs={'CO2_no_sw': hum.co2},
                 q_funcs_args={'CO2_no_sw': (370, 80000)})
-    assert 240 < float(np.ravel(gas.T_g)[0]) < 300
-    assert abs(np.sum(gas.net_flux)) < 1.0
+    # the unmodified reference, same call (Newton on the isothermal column, then the spectral grid
+    # and optical depth are rebuilt for the new T_g, so the sum is no longer exactly zero)
+    assert abs(float(np.ravel(gas.T_g)[0]) - 259.8448678790483) < 1e-8
+    assert abs(np.sum(gas.net_flux) - (-7.506481761631903)) < 1e-8
