@@ -1,6 +1,7 @@
 // Host drivers of the flux path: level-table construction, plan-grid optical depth, and the
 // cmb200_flux / cmb200_flux_host entry points (RealGas.get_flux + net flux + heating rate).
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 #include "flux_kernels.cuh"
@@ -32,7 +33,10 @@ static int ensure_tidx(cmb200_plan *p, int64_t n_col, const double *T_tau, const
 
 // Relative cost of one pass of the flux kernel, used to balance the warps of a CTA: a long-wave
 // pass carries the emission recurrences, and every (part, band) run ends with a replay-only pass.
-static const double kCostLW = 1.5, kCostRun = 0.4;
+static double cost_knob(const char *name, double dflt) {
+    const char *e = getenv(name);
+    return e && *e ? atof(e) : dflt;
+}
 
 // Work decomposition: W warps per CTA (from the shared-memory budget), C CTAs per column (more
 // than one only when there are fewer columns than resident CTAs), parts = C * W contiguous runs
@@ -47,6 +51,7 @@ static int ensure_partition(cmb200_plan *p, int64_t n_col, int W, int resident_c
         C = (int)std::max<int64_t>(1, std::min(want, most));
     }
     const int parts = C * W, n_seg = p->n_seg;
+    const double kCostLW = cost_knob("CMB200_COST_LW", 1.5), kCostRun = cost_knob("CMB200_COST_RUN", 0.4);
     std::vector<double> prefix(n_seg + 1, 0.0);
     for (int s = 0; s < n_seg; ++s) {
         const int j = p->hseg_band[s];
@@ -82,6 +87,9 @@ static int ensure_partition(cmb200_plan *p, int64_t n_col, int W, int resident_c
     CMB_CUDA(pt.part_seg0.upload(seg0.data(), seg0.size()));
     CMB_CUDA(pt.part_slot0.upload(slot0.data(), slot0.size()));
     CMB_CUDA(pt.band_slot0.upload(bslot.data(), bslot.size()));
+    std::vector<double> sdelta(slot_band.size() + 1, 0.0);
+    for (size_t q = 0; q < slot_band.size(); ++q) sdelta[q] = p->hdelta[slot_band[q]];
+    CMB_CUDA(pt.slot_delta.upload(sdelta.data(), sdelta.size()));
     CMB_CUDA(cudaDeviceSynchronize());
     pt.n_col = n_col;
     return CMB200_OK;
@@ -164,6 +172,7 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     a.part_seg0 = pt.part_seg0.p;
     a.part_slot0 = pt.part_slot0.p;
     a.band_slot0 = pt.band_slot0.p;
+    a.slot_delta = pt.slot_delta.p;
     a.pc = PlanckConst{p->c.h_planck, p->c.speed_of_light, p->c.k_boltzmann};
     a.T_star = p->T_star;
     a.star_geom = p->R_star * p->R_star / (p->dist * p->dist);
@@ -188,8 +197,31 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     a.scratch = p->scratch.p;
     a.coefbuf = (Real *)p->coefbuf.p;
 
+    const bool debug_timing = getenv("CMB200_DEBUG_TIMING") != nullptr;
+    DevBuf<long long> dbg;
+    if (debug_timing) {
+        CMB_CUDA(dbg.alloc(64));
+        a.dbg = dbg.p;
+    }
     flux_kernel<Real, MM><<<(unsigned)grid, W * 32, smem, s>>>(a);
     CMB_LAUNCHED();
+    if (debug_timing) {   // per-warp sweep cycles of CTA 0's first column next to what the partition gave each warp
+        long long h[64];
+        CMB_CUDA(cudaStreamSynchronize(s));
+        CMB_CUDA(cudaMemcpy(h, dbg.p, sizeof(h), cudaMemcpyDeviceToHost));
+        std::vector<int32_t> seg0(pt.parts + 1);
+        CMB_CUDA(cudaMemcpy(seg0.data(), pt.part_seg0.p, seg0.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
+        for (int w = 0; w < W; ++w) {
+            int n_sw = 0, n_lw = 0, r_sw = 0, r_lw = 0, last = -1;
+            for (int q = seg0[w]; q < seg0[w + 1]; ++q) {
+                const int j = p->hseg_band[q];
+                (p->hsw[j] ? n_sw : n_lw)++;
+                if (j != last) (p->hsw[j] ? r_sw : r_lw)++;
+                last = j;
+            }
+            fprintf(stderr, "cmb200 timing: warp %d sweep %lld (prologue %lld, whole task %lld)  fresh sw %d lw %d  runs sw %d lw %d\n", w, h[w], h[32 + w], h[48 + w], n_sw, n_lw, r_sw, r_lw);
+        }
+    }
     if (C > 1) {
         flux_finalize_kernel<<<(unsigned)io->n_col, 128, L * sizeof(double), s>>>(
             L, p->B, p->band_lo, p->band_hi, pt.n_slots, io->n_col, pt.band_slot0.p, p->band_delta.p,

@@ -42,6 +42,7 @@ struct FluxArgs {
     const Real *wchain;
     const int64_t *chain_off;
     const int32_t *seg_band, *seg_c0, *part_seg0, *part_slot0, *band_slot0;
+    const double *slot_delta;  // band width of the band each partial-sum slot belongs to
     PlanckConst pc;
     double T_star, star_geom, g, g_over_cp;
     // per column
@@ -57,6 +58,7 @@ struct FluxArgs {
     // work space (written and re-read inside the kernel: never const / restrict)
     double *scratch;           // [region][n_slots][2][L] partial band sums
     Real *coefbuf;             // [CTA][B][4][Lp] emission coefficients of the long-wave bands
+    long long *dbg;            // optional: sweep cycles per warp of CTA 0's first task (CMB200_DEBUG_TIMING)
 };
 
 constexpr int kU = 8;          // layers per block of a pass (instruction-level parallelism)
@@ -285,18 +287,28 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
     };
     auto C4 = [&]() { c1 += __shfl_xor_sync(full, c1, 2); };
     auto C5 = [&]() { c1 += __shfl_xor_sync(full, c1, 1); };
+    // band accumulator of the reduced block: fetched early so that the read latency is off the tail
+    double bold = 0.0;
+    auto Cload = [&](int kc) {
+        if (rlane && kc + ridx < nl) bold = bacc[kc + ridx];
+    };
     auto Cstore = [&](int kc) {
-        if (rlane && kc + ridx < nl) bacc[kc + ridx] += (double)c1;
+        if (rlane && kc + ridx < nl) bacc[kc + ridx] = bold + (double)c1;
     };
 
     // ---- recurrence step of layer kb+u for both chains (stage B) --------------------------------------
     Real EF = wF * b0, HF = Real(0), ER = wR * b0, HR = Real(0);
     Real tp[kU], tR[kU];
+    // Long-wave emission coefficients live in global memory (L2): one coalesced load per block, a
+    // block ahead, gives lane 8 r + i the coefficient of row r (coefL, coefG = coefL + Lp) and layer
+    // k0 + i; the recurrence broadcasts them with shuffles.
+    const Real *crow = coefL + ((lane >> 3) & 1) * (coefG - coefL) + (lane & (kU - 1));
+    Real ccur = Real(0), cnext = Real(0);
     auto Bstep = [&](int kb, int u, Real(&out)[kU]) {
         Real cl = Real(0), cg = Real(0), valF = Real(0), valR;
         if (LW) {
-            cl = coefL[kb + u];
-            cg = coefG[kb + u];
+            cl = __shfl_sync(full, ccur, u);        // lanes 0-7 hold the block's "last/first" row, 8-15 its "gen" row
+            cg = __shfl_sync(full, ccur, kU + u);
         }
         if constexpr (FRESH) {
             EF *= tp[u];
@@ -351,10 +363,21 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
         }
         load_block(kfirst);
 
+        // t-store traffic of a block, spread over the iteration: once the recurrences are done with
+        // layer kb+u the fresh t (still in tp) is parked in its row, and once they are done with the
+        // whole block the replay chain's t of block k0 is fetched from the rows that block k0's fresh t
+        // will overwrite one iteration later.
+        auto park = [&](int kb, int u) { tsl[(kb + u) * 32] = tp[u]; };
+        auto fetch_replay = [&](int k0) {
+#pragma unroll
+            for (int u = 0; u < kU; ++u) tR[u] = tsl[(k0 + u) * 32];
+        };
         auto iter = [&](auto doA_t, auto doB_t, const int k0) {
             constexpr bool DO_A = decltype(doA_t)::value, DO_B = decltype(doB_t)::value;
             const int kb = k0 - kstep;
             Real x[kU], t[kU];
+            if (DO_B) Cload(kb);
+            if (LW && DO_A) cnext = crow[k0];
             // stage A set-up: layer integrand at the block's interfaces, next block's loads, dtau
             if (DO_A) {
                 Src In[kU];
@@ -396,7 +419,7 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
                         tn[u] = fma(-x[u], kExpC[11], kExpC[12]);
                     }
                 }
-                if (DO_B) { Bstep(kb, ord(0), v); Bstep(kb, ord(1), v); }
+                if (DO_B) { Bstep(kb, ord(0), v); Bstep(kb, ord(1), v); park(kb, ord(0)); park(kb, ord(1)); }
                 if (DO_A) {
 #pragma unroll
                     for (int u = 0; u < kU; ++u) {
@@ -404,12 +427,12 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
                         tn[u] -= kExpC[12];
                     }
                 }
-                if (DO_B) { Bstep(kb, ord(2), v); Bstep(kb, ord(3), v); }
+                if (DO_B) { Bstep(kb, ord(2), v); Bstep(kb, ord(3), v); park(kb, ord(2)); park(kb, ord(3)); }
                 if (DO_A) {
 #pragma unroll
                     for (int u = 0; u < kU; ++u) r[u] = fma(tn[u], kExpC[13], -x[u]);
                 }
-                if (DO_B) { Bstep(kb, ord(4), v); Bstep(kb, ord(5), v); }
+                if (DO_B) { Bstep(kb, ord(4), v); Bstep(kb, ord(5), v); park(kb, ord(4)); park(kb, ord(5)); }
                 if (DO_A) {
 #pragma unroll
                     for (int u = 0; u < kU; ++u) {
@@ -417,7 +440,8 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
                         p[u] = kExpC[0];
                     }
                 }
-                if (DO_B) { Bstep(kb, ord(6), v); Bstep(kb, ord(7), v); }
+                if (DO_B) { Bstep(kb, ord(6), v); Bstep(kb, ord(7), v); park(kb, ord(6)); park(kb, ord(7)); }
+                if (DO_A) fetch_replay(k0);
 #pragma unroll
                 for (int i = 1; i <= 10; ++i) {
                     if (DO_A) {
@@ -446,19 +470,19 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
                 }
                 if (DO_B) {
 #pragma unroll
-                    for (int o = 0; o < kU; ++o) Bstep(kb, ord(o), v);
-                    C1(); C2(); C3(); C4(); C5();
+                    for (int o = 0; o < kU; ++o) {
+                        Bstep(kb, ord(o), v);
+                        park(kb, ord(o));
+                    }
                 }
+                if (DO_A) fetch_replay(k0);
+                if (DO_B) { C1(); C2(); C3(); C4(); C5(); }
             }
             if (DO_B) Cstore(kb);
-            if (DO_A) {   // swap the block's t-store rows: out comes the replay chain's t, in goes the fresh one
+            if (DO_A) {
 #pragma unroll
-                for (int u = 0; u < kU; ++u) {
-                    Real *slot = tsl + (k0 + u) * 32;
-                    tR[u] = *slot;
-                    *slot = t[u];
-                    tp[u] = t[u];
-                }
+                for (int u = 0; u < kU; ++u) tp[u] = t[u];
+                ccur = cnext;
             }
         };
         iter(std::true_type{}, std::false_type{}, kfirst);
@@ -474,9 +498,11 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
         Real tn8[kU], vp[kU];
         auto iter = [&](auto doB_t, auto doC_t, const int k0) {
             constexpr bool DO_B = decltype(doB_t)::value, DO_C = decltype(doC_t)::value;
+            if (DO_C) Cload(k0 - kstep);
             if (DO_B && (UP ? k0 >= kU : k0 + kU < Lp)) {
 #pragma unroll
                 for (int u = 0; u < kU; ++u) tn8[u] = tsl[(k0 + kstep + u) * 32];
+                if (LW) cnext = crow[k0 + kstep];
             }
             if (DO_B) Bstep(k0, ord(0), vp);
             if (DO_C) C1();
@@ -497,10 +523,12 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
                     v[u] = vp[u];
                     tR[u] = tn8[u];
                 }
+                ccur = cnext;
             }
         };
 #pragma unroll
         for (int u = 0; u < kU; ++u) tR[u] = tsl[(kfirst + u) * 32];
+        if (LW) ccur = crow[kfirst];
         iter(std::true_type{}, std::false_type{}, kfirst);
         if (UP) {
             for (int k0 = Lp - 2 * kU; k0 >= 0; k0 -= kU) iter(std::true_type{}, std::true_type{}, k0);
@@ -565,6 +593,7 @@ __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
         const int cpart = (int)(task - col * C);
         const int64_t region = C == 1 ? (int64_t)blockIdx.x : col;
         __syncthreads();   // the previous task is done with the tables, the scratch and sacc
+        const long long t_task0 = a.dbg ? clock64() : 0;
 
         // ---- the column's level tables ---------------------------------------------------------------
         for (int idx = tid; idx < MR * lstride; idx += nthr) {
@@ -586,23 +615,47 @@ __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
         const int sA = a.part_seg0[cpart * W], sB = a.part_seg0[(cpart + 1) * W];
         const double Tg = a.T_g[col];
         if (sA < sB) {
+            // Lane = one layer of a 31-layer chunk (lane 31 only supplies B at the next interface); the
+            // warps that share a chunk take every other long-wave band.  Temperatures and the pressure
+            // weights of the layer are fetched once, and the bands are walked two at a time so that the
+            // Planck evaluations (exp + divide, latency bound) overlap.
             const int jA = a.seg_band[sA], jB = a.seg_band[sB - 1];
-            const int nch = (nl + 30) / 31;                       // 31 layers per warp: lane 31 only feeds B(k+1)
-            for (int wt = warp; wt < (jB - jA + 1) * nch; wt += W) {
-                const int j = jA + wt / nch, k = (wt % nch) * 31 + lane;
-                if (a.band_sw[j]) continue;
-                const double c = a.band_centre[j];
-                double bi = 0.0, bc = 0.0;
-                if (k < L) bi = M_PI * planck_wavenumber(a.pc, c, k == L - 1 ? Tg : a.Tint[col * L + k]);      // :636
-                if (k < nl) bc = M_PI * planck_wavenumber(a.pc, c, a.T[col * nl + k]);
-                const double bi1 = __shfl_down_sync(0xffffffffu, bi, 1);
-                if (lane < 31 && k < nl) {
-                    const double *g0 = a.geo + k;
-                    Real *cf = coef_cta + (size_t)j * 4 * Lp + k;
-                    cf[0] = (Real)(g0[0] * bi + g0[nl] * bc + g0[2 * nl] * bi1);                 // dn_last
-                    cf[Lp] = (Real)(g0[3 * nl] * bi + g0[4 * nl] * bc);                          // dn_gen
-                    cf[2 * Lp] = (Real)(g0[5 * nl] * bi + g0[6 * nl] * bc + g0[7 * nl] * bi1);   // up_first
-                    cf[3 * Lp] = (Real)(g0[8 * nl] * bc + g0[9 * nl] * bi1);                     // up_gen
+            const int nch = (nl + 30) / 31, chs = min(W, nch), groups = W / chs, grp = warp / chs;
+            for (int ch = warp % chs; grp < groups && ch < nch; ch += chs) {
+                const int k = ch * 31 + lane;
+                const double Ti = k < L ? (k == L - 1 ? Tg : a.Tint[col * L + k]) : 1.0;      // :636
+                const double Tc = k < nl ? a.T[col * nl + k] : 1.0;
+                const bool writer = lane < 31 && k < nl;
+                double gw[10];
+#pragma unroll
+                for (int r = 0; r < 10; ++r) gw[r] = writer ? __ldg(a.geo + r * nl + k) : 0.0;
+                auto one_band = [&](int j, double bi, double bc) {
+                    const double bi1 = __shfl_down_sync(0xffffffffu, bi, 1);
+                    if (writer) {
+                        Real *cf = coef_cta + (size_t)j * 4 * Lp + k;
+                        cf[0] = (Real)(gw[0] * bi + gw[1] * bc + gw[2] * bi1);        // dn_last
+                        cf[Lp] = (Real)(gw[3] * bi + gw[4] * bc);                     // dn_gen
+                        cf[2 * Lp] = (Real)(gw[5] * bi + gw[6] * bc + gw[7] * bi1);   // up_first
+                        cf[3 * Lp] = (Real)(gw[8] * bc + gw[9] * bi1);                // up_gen
+                    }
+                };
+                int pend = -1;                                      // a long-wave band waiting for a partner
+                for (int j = jA + grp; j <= jB; j += groups) {
+                    if (__ldg(a.band_sw + j)) continue;
+                    if (pend < 0) {
+                        pend = j;
+                        continue;
+                    }
+                    const double c0 = __ldg(a.band_centre + pend), c1 = __ldg(a.band_centre + j);
+                    const double bi0 = M_PI * planck_wavenumber(a.pc, c0, Ti), bi1 = M_PI * planck_wavenumber(a.pc, c1, Ti);
+                    const double bc0 = M_PI * planck_wavenumber(a.pc, c0, Tc), bc1 = M_PI * planck_wavenumber(a.pc, c1, Tc);
+                    one_band(pend, bi0, bc0);
+                    one_band(j, bi1, bc1);
+                    pend = -1;
+                }
+                if (pend >= 0) {
+                    const double c0 = __ldg(a.band_centre + pend);
+                    one_band(pend, M_PI * planck_wavenumber(a.pc, c0, Ti), M_PI * planck_wavenumber(a.pc, c0, Tc));
                 }
             }
         }
@@ -617,6 +670,7 @@ __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
         const int s1 = a.part_seg0[part + 1];
         int slot = a.part_slot0[part];
         bool up = false;
+        const long long t_sweep0 = a.dbg ? clock64() : 0;
         while (s < s1) {
             const int j = a.seg_band[s];
             int e = s + 1;
@@ -655,6 +709,11 @@ __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
             for (int i = lane; i < 2 * LS; i += 32) bacc_up[i] = 0.0;
             __syncwarp();
         }
+        const bool dbg_here = a.dbg && task == (int64_t)blockIdx.x + gridDim.x * (int64_t)(a.n_tasks / gridDim.x / 2) && blockIdx.x == 0 && lane == 0;
+        if (dbg_here) {
+            a.dbg[warp] = clock64() - t_sweep0;
+            a.dbg[32 + warp] = t_sweep0 - t_task0;
+        }
         if (C != 1) continue;      // several CTAs per column: flux_finalize_kernel adds the slots up
 
         // ---- column epilogue: band sums, net flux (:712-713), heating rate (base.py:166-168) ----------
@@ -664,6 +723,21 @@ __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
             const int half = idx >= L, i = idx - half * L;
             double *out = half ? a.down : a.up;
             double acc = 0.0;
+            if (!out) {     // only net / heating wanted: independent loads, slot by slot
+                const double *v = sc + half * (int64_t)L + i;
+                int q = 0;
+                for (; q + 8 <= a.n_slots; q += 8) {
+                    double x[8], d[8];
+#pragma unroll
+                    for (int r = 0; r < 8; ++r) {
+                        x[r] = v[(q + r) * 2 * (int64_t)L];
+                        d[r] = __ldg(a.slot_delta + q + r);
+                    }
+#pragma unroll
+                    for (int r = 0; r < 8; ++r) acc = fma(x[r], d[r], acc);
+                }
+                for (; q < a.n_slots; ++q) acc = fma(v[q * 2 * (int64_t)L], __ldg(a.slot_delta + q), acc);
+            } else
             for (int j = a.band_lo; j < a.band_hi; ++j) {
                 double sum = 0.0;
                 const int q0 = a.band_slot0[j], q1 = a.band_slot0[j + 1];
@@ -684,6 +758,7 @@ __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
         }
         __syncthreads();
         for (int idx = tid; idx < 2 * L; idx += nthr) sacc[idx] = 0.0;
+        if (dbg_here) a.dbg[48 + warp] = clock64() - t_task0;
     }
 }
 

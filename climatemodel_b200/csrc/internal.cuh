@@ -22,6 +22,7 @@ struct Partition {
     int parts = 0;          // C * W contiguous, cost-balanced runs of segments per column
     int n_slots = 0;        // partial-sum slots per column: one per (part, band) run
     DevBuf<int32_t> part_seg0, part_slot0, band_slot0;
+    DevBuf<double> slot_delta;
 };
 
 }  // namespace cmb

@@ -27,8 +27,13 @@ KEYS = [
 
 
 def page(rep, name):
-    out = subprocess.run(['ncu', '-i', rep, '--page', name, '--csv'], capture_output=True, text=True).stdout
-    return list(csv.reader(io.StringIO(out)))
+    extra = []
+    out = subprocess.run(['ncu', '-i', rep, '--page', name, '--csv'] + extra, capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(out)))
+    if name == 'source':        # drop the leading "Kernel Name" record
+        while rows and 'Source' not in rows[0]:
+            rows.pop(0)
+    return rows
 
 
 def main():
