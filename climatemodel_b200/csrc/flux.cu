@@ -167,6 +167,8 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     a.band_sw = p->band_sw.p;
     a.wchain = std::is_same<Real, double>::value ? (const Real *)p->wchain64.p : (const Real *)p->wchain32.p;
     a.chain_off = p->chain_off.p;
+    a.seg_w = std::is_same<Real, double>::value ? (const Real *)p->seg_w64.p : (const Real *)p->seg_w32.p;
+    a.seg_bin = p->seg_bin.p;
     a.seg_band = p->seg_band.p;
     a.seg_c0 = p->seg_c0.p;
     a.part_seg0 = pt.part_seg0.p;
@@ -196,6 +198,9 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     a.heating = io->heating;
     a.scratch = p->scratch.p;
     a.coefbuf = (Real *)p->coefbuf.p;
+    if (!p->task_counter.p) CMB_CUDA(p->task_counter.alloc(1));
+    CMB_CUDA(cudaMemsetAsync(p->task_counter.p, 0, sizeof(unsigned long long), s));
+    a.task_counter = p->task_counter.p;
 
     const bool debug_timing = getenv("CMB200_DEBUG_TIMING") != nullptr;
     DevBuf<long long> dbg;

@@ -39,7 +39,8 @@ struct FluxArgs {
     const int32_t *band_start, *band_len;
     const double *band_centre, *band_delta, *band_sumw;
     const uint8_t *band_sw;
-    const Real *wchain;
+    const Real *wchain, *seg_w;   // nu-weights per chain; the same per (segment, lane)
+    const int32_t *seg_bin;       // wavenumber bin per (segment, lane)
     const int64_t *chain_off;
     const int32_t *seg_band, *seg_c0, *part_seg0, *part_slot0, *band_slot0;
     const double *slot_delta;  // band width of the band each partial-sum slot belongs to
@@ -58,6 +59,7 @@ struct FluxArgs {
     // work space (written and re-read inside the kernel: never const / restrict)
     double *scratch;           // [region][n_slots][2][L] partial band sums
     Real *coefbuf;             // [CTA][B][4][Lp] emission coefficients of the long-wave bands
+    unsigned long long *task_counter;   // zeroed before the launch
     long long *dbg;            // optional: sweep cycles per warp of CTA 0's first task (CMB200_DEBUG_TIMING)
 };
 
@@ -234,6 +236,33 @@ __device__ __forceinline__ Real reduce8(const Real (&v)[8], int lane) {
     return c;
 }
 
+// Table values (or tau) a fresh pass starts from, fetched while the pass before it is still running:
+// the loaded interfaces of its first block and the raw values behind the carried interface.
+template <typename Real, int MM>
+struct PassFeed {
+    using Src = typename std::conditional<(MM > 0), Real, double>::type;
+    Src raw[kU][MM > 0 ? MM : 1];
+    Src icraw[MM > 0 ? MM : 1];
+};
+template <typename Real, int MM>
+__device__ __forceinline__ void prefetch_pass(const bool up, const int Lp, const void *src_lane,
+                                              const LevelView<Real> &lv, PassFeed<Real, MM> &fd) {
+    using Src = typename PassFeed<Real, MM>::Src;
+    constexpr int MR = MM > 0 ? MM : 1;
+    constexpr unsigned kOffUnit = MM > 0 ? 16u : 8u;
+    const char *src_bytes = (const char *)src_lane;
+    const unsigned *offs = up ? lv.off_up : lv.off_dn;
+    const int k0 = up ? Lp - kU : 0, kc = (up ? Lp : 0) + kLevShift;
+#pragma unroll
+    for (int m = 0; m < MR; ++m) {
+        unsigned off[kU];
+        lds_block(offs + m * lv.stride + k0 + 4, off);
+#pragma unroll
+        for (int u = 0; u < kU; ++u) fd.raw[u][m] = *(const Src *)(src_bytes + (size_t)off[u] * kOffUnit);
+        fd.icraw[m] = *(const Src *)(src_bytes + (size_t)lv.off_dn[m * lv.stride + kc] * kOffUnit);
+    }
+}
+
 // One pass over the levels for the (up to) two chains this lane holds.
 //   UP = false: TOA -> surface, value of layer k belongs to interface k+1 (caller passes bacc_dn + 1)
 //   UP = true:  surface -> TOA, value of layer k belongs to interface k   (caller passes bacc_up)
@@ -251,8 +280,9 @@ __device__ __forceinline__ Real reduce8(const Real (&v)[8], int lane) {
 // in between, statement by statement -- ptxas keeps this order.
 template <typename Real, int MM, bool LW, bool UP, bool FRESH>
 __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const int Lp, const Real wF, const Real wR,
-                                           const Real b0, const void *src_lane, const LevelView<Real> lv, Real *tsl,
-                                           double *bacc, const Real *coefL, const Real *coefG) {
+                                           const Real b0, const void *src_lane, const void *next_src,
+                                           PassFeed<Real, MM> &fd, const LevelView<Real> lv, Real *tsl, double *bacc,
+                                           const Real *coefL, const Real *coefG) {
     constexpr bool FUSED = MM > 0;
     constexpr int MR = MM > 0 ? MM : 1;
     constexpr bool F64 = sizeof(Real) == 8;
@@ -338,7 +368,7 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
         // raw[u][m]: table value (or tau) of the block's loaded interfaces, fetched one block ahead so
         // that the L2 / HBM latency hides behind the previous block's work.
         const unsigned *offs = UP ? lv.off_up : lv.off_dn;   // either way the group of block k0 starts at k0 + 4
-        Src raw[kU][MR];
+        auto &raw = fd.raw;                                  // first block already in flight (prefetch_pass)
         auto ld = [&](unsigned off) { return *(const Src *)(src_bytes + (size_t)off * kOffUnit); };
         auto load_block = [&](int k0) {
 #pragma unroll
@@ -350,18 +380,14 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
             }
         };
         Src Ic;                                               // the carried interface of the next block
-        {
-            const int k = (UP ? Lp : 0) + kLevShift;
-            if (FUSED) {
-                Real acc = Real(0);
+        if (FUSED) {
+            Real acc = Real(0);
 #pragma unroll
-                for (int m = 0; m < MR; ++m) acc += lv.qg[m * lv.stride + k] * (Real)ld(lv.off_dn[m * lv.stride + k]);
-                Ic = (Src)acc;
-            } else {
-                Ic = ld(lv.off_dn[k]);
-            }
+            for (int m = 0; m < MR; ++m) acc += lv.qg[m * lv.stride + (UP ? Lp : 0) + kLevShift] * (Real)fd.icraw[m];
+            Ic = (Src)acc;
+        } else {
+            Ic = fd.icraw[0];
         }
-        load_block(kfirst);
 
         // t-store traffic of a block, spread over the iteration: once the recurrences are done with
         // layer kb+u the fresh t (still in tp) is parked in its row, and once they are done with the
@@ -488,9 +514,11 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
         iter(std::true_type{}, std::false_type{}, kfirst);
         if (UP) {
             for (int k0 = Lp - 2 * kU; k0 >= 0; k0 -= kU) iter(std::true_type{}, std::true_type{}, k0);
+            if (next_src) prefetch_pass<Real, MM>(!UP, Lp, next_src, lv, fd);   // raw is free from here on
             iter(std::false_type{}, std::true_type{}, -kU);
         } else {
             for (int k0 = kU; k0 < Lp; k0 += kU) iter(std::true_type{}, std::true_type{}, k0);
+            if (next_src) prefetch_pass<Real, MM>(!UP, Lp, next_src, lv, fd);   // raw is free from here on
             iter(std::false_type{}, std::true_type{}, Lp);
         }
     } else {
@@ -527,6 +555,7 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
             }
         };
 #pragma unroll
+        if (next_src) prefetch_pass<Real, MM>(!UP, Lp, next_src, lv, fd);
         for (int u = 0; u < kU; ++u) tR[u] = tsl[(kfirst + u) * 32];
         if (LW) ccur = crow[kfirst];
         iter(std::true_type{}, std::false_type{}, kfirst);
@@ -543,19 +572,20 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
 template <typename Real, int MM, bool FRESH>
 __device__ __forceinline__ void dispatch_pass(const bool lw, const bool up, const int lane, const int nl, const int Lp,
                                               const Real wF, const Real wR, const Real bs, const Real bg,
-                                              const void *src_lane, const LevelView<Real> &lv, Real *tsl,
-                                              double *bacc_up, double *bacc_dn, const Real *coef) {
+                                              const void *src_lane, const void *next_src, PassFeed<Real, MM> &fd,
+                                              const LevelView<Real> &lv, Real *tsl, double *bacc_up, double *bacc_dn,
+                                              const Real *coef) {
     // coefficient rows of a band: [0] dn_last, [1] dn_gen, [2] up_first, [3] up_gen
     if (lw) {
         if (up)
-            sweep_pass<Real, MM, true, true, FRESH>(lane, nl, Lp, wF, wR, bg, src_lane, lv, tsl, bacc_up, coef + 2 * Lp, coef + 3 * Lp);
+            sweep_pass<Real, MM, true, true, FRESH>(lane, nl, Lp, wF, wR, bg, src_lane, next_src, fd, lv, tsl, bacc_up, coef + 2 * Lp, coef + 3 * Lp);
         else
-            sweep_pass<Real, MM, true, false, FRESH>(lane, nl, Lp, wF, wR, bs, src_lane, lv, tsl, bacc_dn + 1, coef, coef + Lp);
+            sweep_pass<Real, MM, true, false, FRESH>(lane, nl, Lp, wF, wR, bs, src_lane, next_src, fd, lv, tsl, bacc_dn + 1, coef, coef + Lp);
     } else {
         if (up)
-            sweep_pass<Real, MM, false, true, FRESH>(lane, nl, Lp, wF, wR, bg, src_lane, lv, tsl, bacc_up, coef, coef);
+            sweep_pass<Real, MM, false, true, FRESH>(lane, nl, Lp, wF, wR, bg, src_lane, next_src, fd, lv, tsl, bacc_up, coef, coef);
         else
-            sweep_pass<Real, MM, false, false, FRESH>(lane, nl, Lp, wF, wR, bs, src_lane, lv, tsl, bacc_dn + 1, coef, coef);
+            sweep_pass<Real, MM, false, false, FRESH>(lane, nl, Lp, wF, wR, bs, src_lane, next_src, fd, lv, tsl, bacc_dn + 1, coef, coef);
     }
 }
 
@@ -588,11 +618,18 @@ __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
     for (int i = lane; i < 2 * LS; i += 32) bacc_up[i] = 0.0;
     for (int i = lane; i < Lp * 32; i += 32) ts[i] = Real(0);   // the first replay of a run reads it with weight 0
 
-    for (int64_t task = blockIdx.x; task < a.n_tasks; task += gridDim.x) {
+    // Tasks are handed out through a global counter: SMs differ a little in speed (L2 distance,
+    // table rows hit), and a static split would leave the fast ones idle at the end.
+    __shared__ unsigned long long s_task;
+    for (int n_done = 0;; ++n_done) {
+        __syncthreads();   // the previous task is done with the tables, the scratch, sacc and s_task
+        if (tid == 0) s_task = atomicAdd(a.task_counter, 1ULL);
+        __syncthreads();
+        const int64_t task = (int64_t)s_task;
+        if (task >= a.n_tasks) break;
         const int64_t col = task / C;
         const int cpart = (int)(task - col * C);
         const int64_t region = C == 1 ? (int64_t)blockIdx.x : col;
-        __syncthreads();   // the previous task is done with the tables, the scratch and sacc
         const long long t_task0 = a.dbg ? clock64() : 0;
 
         // ---- the column's level tables ---------------------------------------------------------------
@@ -671,6 +708,20 @@ __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
         int slot = a.part_slot0[part];
         bool up = false;
         const long long t_sweep0 = a.dbg ? clock64() : 0;
+        // Parameters of a segment: one chain (wavenumber bin of its band) per lane.  They, and the
+        // first table rows of the pass, are fetched one pass ahead so that no pass starts on a miss.
+        auto seg_params = [&](int sidx, Real &w, const void *&src) {
+            w = __ldg(a.seg_w + (int64_t)sidx * 32 + lane);
+            const int64_t n = __ldg(a.seg_bin + (int64_t)sidx * 32 + lane);
+            src = FUSED ? (const void *)(a.KL + n) : (const void *)(tau_col + n);
+        };
+        PassFeed<Real, MM> fd;
+        Real wN = Real(0);
+        const void *srcN = nullptr;
+        if (s < s1) {
+            seg_params(s, wN, srcN);
+            prefetch_pass<Real, MM>(up, Lp, srcN, lv, fd);
+        }
         while (s < s1) {
             const int j = a.seg_band[s];
             int e = s + 1;
@@ -685,17 +736,17 @@ __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
                 bacc_dn[0] += (double)bs * a.band_sumw[j];
             }
             Real wR = Real(0);
-            for (; s < e; ++s) {                   // one chain (wavenumber bin of band j) per lane
-                const int ci = a.seg_c0[s] + lane;
-                const bool act = ci < a.band_len[j];
-                const Real wF = act ? a.wchain[a.chain_off[j] + ci] : Real(0);
-                const int64_t n = a.band_start[j] + (act ? ci : 0);
-                const void *src_lane = FUSED ? (const void *)(a.KL + n) : (const void *)(tau_col + n);
-                dispatch_pass<Real, MM, true>(lw, up, lane, nl, Lp, wF, wR, bs, bg, src_lane, lv, ts + lane, bacc_up, bacc_dn, coef);
+            for (; s < e; ++s) {
+                const Real wF = wN;
+                const void *src_lane = srcN;
+                if (s + 1 < s1) seg_params(s + 1, wN, srcN);
+                dispatch_pass<Real, MM, true>(lw, up, lane, nl, Lp, wF, wR, bs, bg, src_lane, s + 1 < e ? srcN : nullptr, fd, lv,
+                                              ts + lane, bacc_up, bacc_dn, coef);
                 wR = wF;
                 up = !up;
             }
-            dispatch_pass<Real, MM, false>(lw, up, lane, nl, Lp, Real(0), wR, bs, bg, nullptr, lv, ts + lane, bacc_up, bacc_dn, coef);
+            dispatch_pass<Real, MM, false>(lw, up, lane, nl, Lp, Real(0), wR, bs, bg, nullptr, s < s1 ? srcN : nullptr, fd, lv,
+                                           ts + lane, bacc_up, bacc_dn, coef);
             up = !up;
             // ---- partial band sums of this (warp, band) run -> scratch slot ---------------------------
             __syncwarp();
@@ -709,7 +760,7 @@ __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
             for (int i = lane; i < 2 * LS; i += 32) bacc_up[i] = 0.0;
             __syncwarp();
         }
-        const bool dbg_here = a.dbg && task == (int64_t)blockIdx.x + gridDim.x * (int64_t)(a.n_tasks / gridDim.x / 2) && blockIdx.x == 0 && lane == 0;
+        const bool dbg_here = a.dbg && n_done == (int)(a.n_tasks / gridDim.x / 2) && blockIdx.x == 0 && lane == 0;
         if (dbg_here) {
             a.dbg[warp] = clock64() - t_sweep0;
             a.dbg[32 + warp] = t_sweep0 - t_task0;

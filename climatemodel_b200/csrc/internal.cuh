@@ -51,8 +51,12 @@ struct cmb200_plan {
     cmb::DevBuf<int64_t> chain_off;
     int64_t n_chains = 0;
     // device: segments (runs of 32*kChains bins inside one band) for bands [band_lo, band_hi)
-    cmb::DevBuf<int32_t> seg_band, seg_c0;
+    cmb::DevBuf<int32_t> seg_band, seg_c0, seg_bin;   // seg_bin[n_seg][32]: wavenumber bin of each lane's chain
+    cmb::DevBuf<double> seg_w64;                      // seg_w[n_seg][32]: its nu-weight (0 for idle lanes)
+    cmb::DevBuf<float> seg_w32;
     std::vector<int32_t> hseg_band, hseg_c0;
+    std::vector<double> hwchain;      // nu-weights of all chains, band after band
+    std::vector<int64_t> hchain_off;
     int n_seg = 0;
     // device: level table KL[M][L][nT_pad][pitch]
     int M = 0, nT_pad = 0;
@@ -64,6 +68,7 @@ struct cmb200_plan {
     // per-call scratch kept between calls (grown on demand)
     cmb::DevBuf<double> Tint, scratch, coefbuf;
     cmb::DevBuf<uint8_t> tidx;
+    cmb::DevBuf<unsigned long long> task_counter;
 };
 
 namespace cmb {

@@ -157,6 +157,23 @@ int build_segments(cmb200_plan *p) {
     p->hseg_c0 = sc;
     CMB_CUDA(p->seg_band.upload(sb.data(), sb.size()));
     CMB_CUDA(p->seg_c0.upload(sc.data(), sc.size()));
+    // per-lane chain of every segment, flat, so that the kernel fetches a segment with two coalesced loads
+    std::vector<int32_t> bin(sb.size() * 32 + 32, 0);
+    std::vector<double> w64(sb.size() * 32 + 32, 0.0);
+    std::vector<float> w32(sb.size() * 32 + 32, 0.f);
+    for (size_t s = 0; s < sb.size(); ++s)
+        for (int lane = 0; lane < 32; ++lane) {
+            const int j = sb[s], ci = sc[s] + lane;
+            const bool act = ci < p->hlen[j];
+            bin[s * 32 + lane] = p->hstart[j] + (act ? ci : 0);
+            if (act && !p->hwchain.empty()) w64[s * 32 + lane] = p->hwchain[p->hchain_off[j] + ci];
+            w32[s * 32 + lane] = (float)w64[s * 32 + lane];
+        }
+    CMB_CUDA(p->seg_bin.upload(bin.data(), bin.size()));
+    if (p->precision == CMB200_F64)
+        CMB_CUDA(p->seg_w64.upload(w64.data(), w64.size()));
+    else
+        CMB_CUDA(p->seg_w32.upload(w32.data(), w32.size()));
     CMB_CUDA(cudaDeviceSynchronize());
     p->partition.n_col = -1;
     return CMB200_OK;
@@ -268,6 +285,8 @@ extern "C" int cmb200_plan_create(cmb200_plan **plan, int device, int precision,
         delete p;
         return CMB200_ERR_CUDA;
     }
+    p->hwchain = w64;
+    p->hchain_off = off;
     rc = build_segments(p);
     if (rc) {
         delete p;
