@@ -38,6 +38,7 @@ UNIT = 'column*level*bin/s'
 #   exp           : range reduction + degree-11 polynomial + scaling (CUDA exp)     EXP_FLOPS
 #   short-wave    : two running products, two source terms, two weighted sums       8
 #   long-wave     : additionally both emission recurrences                          + 14
+NCU_DRAM_BYTES_PER_COLUMN = (68.546560e6 + 51.996160e6) / 8880    # profiles/r01_flux_kernel_v6_ncu_full.txt
 EXP_FLOPS = {'f64': 36, 'f32': 4}
 
 
@@ -300,6 +301,12 @@ def run_b200(a):
     except Exception:
         pass
     roofline['hbm']['achieved_gbs'] = roofline['hbm']['algorithmic_bytes_per_step'] / (kernel_ms * 1e-3) / 1e9
+    # DRAM traffic of the flux kernel from the committed `ncu --set full` capture (dram__bytes_read.sum +
+    # dram__bytes_write.sum = 120.5 MB for 8880 columns of this workload, profiles/r01_flux_kernel_v6_ncu_full.txt),
+    # scaled per column to this launch; only meaningful for the default FP64 workload shape.
+    if a.precision == 'f64' and (L, M, w['nu'].size) == (100, 2, 10400):
+        roofline['traffic'] = NCU_DRAM_BYTES_PER_COLUMN * n_col / world
+        roofline['traffic_source'] = 'ncu dram bytes per column (8880-column capture) x columns of this launch'
 
     cpu = None
     if world == 1 and not a.no_cpu_baseline:
