@@ -37,6 +37,23 @@ def bands_from_nu_bands(nu, nu_bands):
             'sw': np.asarray(nu_bands['sw']).astype(np.uint8)}
 
 
+def segment_table(band_len, band_sw, bins_per_segment=32):
+    """The kernel's unit of work sharing: runs of ``bins_per_segment`` bins inside a band, numbered
+    band after band.  Returns (band index, is-long-wave flag) of every segment."""
+    per_band = -(-np.asarray(band_len, dtype=np.int64) // bins_per_segment)
+    seg_band = np.repeat(np.arange(len(per_band)), per_band)
+    return seg_band, ~np.asarray(band_sw).astype(bool)[seg_band]
+
+
+def shard_edges(is_lw, world_size, lw_cost=2.5):
+    """Cut the segment list into ``world_size`` contiguous ranges of equal estimated cost (a
+    long-wave segment also runs the emission recurrences and, being alone in its band, pays a
+    replay-only pass).  Returns world_size + 1 edges; rank r owns [edges[r], edges[r + 1])."""
+    cost = np.cumsum(np.where(is_lw, lw_cost, 1.0))
+    inner = [int(np.searchsorted(cost, cost[-1] * r / world_size)) for r in range(1, world_size)]
+    return [0] + inner + [int(np.size(is_lw))]
+
+
 class FluxPlan:
     def __init__(self, P, nu, bands, tables=None, precision='f64', device=0,
                  T_star=None, R_star=None, star_planet_dist=None):
@@ -102,10 +119,9 @@ class FluxPlan:
         """(bins_per_segment, band index of every segment, is-long-wave flag of every segment)."""
         bps, n = C.c_int32(), C.c_int64()
         check(self._lib.cmb200_plan_segments(self._h, C.byref(bps), C.byref(n)))
-        per_band = -(-self.band_len.astype(np.int64) // bps.value)
-        seg_band = np.repeat(np.arange(self.B), per_band)
+        seg_band, is_lw = segment_table(self.band_len, self.band_sw, bps.value)
         assert seg_band.size == n.value
-        return bps.value, seg_band, ~self.band_sw.astype(bool)[seg_band]
+        return bps.value, seg_band, is_lw
 
     def set_segment_range(self, lo, hi):
         check(self._lib.cmb200_plan_set_segment_range(self._h, int(lo), int(hi)))
@@ -115,9 +131,7 @@ class FluxPlan:
         equal estimated cost (a long-wave segment also runs the emission recurrences).  The
         outputs are then partial sums; add them across ranks."""
         _, _, is_lw = self.segments()
-        cost = np.cumsum(np.where(is_lw, lw_cost, 1.0))
-        edges = [0] + [int(np.searchsorted(cost, cost[-1] * r / world_size)) for r in range(1, world_size)] \
-            + [is_lw.size]
+        edges = shard_edges(is_lw, world_size, lw_cost)
         self.set_segment_range(edges[rank], edges[rank + 1])
         return edges[rank], edges[rank + 1]
 

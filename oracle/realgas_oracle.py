@@ -360,10 +360,15 @@ def band_bin_weights(nu, start, length, delta):
 
 
 def get_flux_per_bin(P, T, T_g, integrand, nu, bands, T_star=T_sun, R_star=R_sun, dist=AU,
-                     albedo=0.3, T_interface=None):
+                     albedo=0.3, T_interface=None, segment_range=None, bins_per_segment=32):
     """Same up, down [L, B] as ``get_flux`` but from the layer integrand I[L, N]
     (= sum_mol k q / g on the interfaces) by one exp per (layer, bin) and two linear
-    recurrences over the layers; band sums with the trapezoid nu-weights."""
+    recurrences over the layers; band sums with the trapezoid nu-weights.
+
+    ``segment_range`` = (lo, hi) keeps only the chains of segments lo..hi-1 (runs of
+    ``bins_per_segment`` bins inside a band, numbered band after band) -- the partial sum one rank
+    of a wavenumber-sharded evaluation holds; the boundary terms of a band go with
+    its first segment.  Partial sums over a tiling of the segments add up to the full result."""
     P = np.asarray(P, dtype=float).reshape(-1)
     T = np.asarray(T, dtype=float).reshape(-1)
     L = P.size
@@ -378,6 +383,14 @@ def get_flux_per_bin(P, T, T_g, integrand, nu, bands, T_star=T_sun, R_star=R_sun
     for j in range(B):
         s, n = int(bands['start'][j]), int(bands['len'][j])
         w = band_bin_weights(nu, s, n, bands['delta'][j])
+        w_all = np.sum(w)
+        if segment_range is not None:
+            first = int(np.sum(-(-np.asarray(bands['len'][:j], dtype=np.int64) // bins_per_segment)))
+            seg = first + np.arange(n) // bins_per_segment
+            keep = (seg >= segment_range[0]) & (seg < segment_range[1])
+            w = np.where(keep, w, 0.0)
+            if not (segment_range[0] <= first < segment_range[1]):
+                w_all = 0.0
         I = integrand[:, s:s + n]
         dtau = dP.reshape(-1, 1) * (I[1:] + I[:-1]) / 2.0       # layer optical thickness
         t = np.exp(-dtau)
@@ -394,7 +407,7 @@ def get_flux_per_bin(P, T, T_g, integrand, nu, bands, T_star=T_sun, R_star=R_sun
         # downward sweep, TOA -> surface
         E = np.ones(n)
         H = np.zeros(n)
-        dn[0, j] = bs * np.sum(w)
+        dn[0, j] = bs * w_all
         for k in range(L - 1):
             E = E * t[k]
             val = bs * E
@@ -406,7 +419,7 @@ def get_flux_per_bin(P, T, T_g, integrand, nu, bands, T_star=T_sun, R_star=R_sun
         # upward sweep, surface -> TOA
         E = np.ones(n)
         S = np.zeros(n)
-        up[L - 1, j] = bg * np.sum(w)
+        up[L - 1, j] = bg * w_all
         for i in range(L - 2, -1, -1):
             E = E * t[i]
             val = bg * E
