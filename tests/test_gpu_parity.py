@@ -325,3 +325,48 @@ def test_errors():
         FluxPlan(c['P'][::-1], c['nu'], c['bands'])
     with pytest.raises(ValueError):
         FluxPlan(c['P'][:4], c['nu'], c['bands'])
+
+
+# ---- shapes at the edges of the kernel's decomposition -------------------------------------------------
+@pytest.mark.parametrize('L,M,N,B', [(5, 1, 70, 3), (9, 2, 333, 7), (10, 3, 97, 2), (17, 4, 500, 11),
+                                      (150, 2, 640, 9), (230, 1, 200, 5)])
+def test_shapes_against_oracle(L, M, N, B):
+    """Level counts below / at / off the 8-layer block size and beyond what 8 warps' t-stores fit
+    (fewer warps per CTA), 1-4 molecules, ragged bands (1-bin bands, bands that are not a
+    multiple of 32 bins, a long-wave band spanning several segments), few and many columns, both
+    optical-depth sources: against the oracle's evaluation of the reference algorithm."""
+    rng = np.random.default_rng(100 * L + M)
+    P = np.sort(np.logspace(np.log10(101320.), np.log10(30.), L))
+    nu = 10.0 + np.arange(N) * 7.0
+    cuts = np.sort(rng.choice(np.arange(1, N - 1), B - 1, replace=False))
+    edges = np.concatenate(([0], cuts, [N - 1]))
+    if B >= 3:
+        edges[1] = edges[0] + 1                     # a band of two bins
+    start, stop = edges[:-1], edges[1:]
+    bands = {'start': start.astype(np.int32), 'len': (stop - start + 1).astype(np.int32),
+             'centre': 0.5 * (nu[start] + nu[stop]), 'delta': nu[stop] - nu[start],
+             'sw': (np.arange(B) >= max(1, (2 * B) // 3)).astype(np.uint8)}
+    tabs = [{'p': np.logspace(5.1, 1, 12 + m), 'T': np.linspace(180., 320., 3 + m), 'nu': nu,
+             'absorption_coef': 10 ** rng.uniform(-7, 1, (12 + m, 3 + m, N))} for m in range(M)]
+    from climatemodel_b200.plan import FluxPlan
+    plan = FluxPlan(P, nu, bands, tables=tabs)
+    c = {'P': P, 'nu': nu, 'tables': tabs, 'bands': bands, 'T_star': 5778., 'R_star': 6.96340e8,
+         'dist': 1.495978707e11, 'band_delta': bands['delta']}
+    for n_col in (1, 3, 400):
+        T = 250.0 + rng.normal(0, 8, (n_col, L - 1))
+        T_g = 260.0 + rng.normal(0, 5, n_col)
+        T_tau = 250.0 + rng.uniform(-80, 80, (n_col, L))
+        q = 10 ** rng.uniform(-6, -2, (M, n_col, L))
+        albedo = rng.uniform(0.1, 0.6, n_col)
+        out = plan.flux(T, T_g, T_tau=T_tau, q=q, albedo=albedo)
+        for i in sorted({0, n_col // 2, n_col - 1}):
+            up, dn, net, heat = oracle_column(c, T[i], T_g[i], T_tau[i], albedo[i], q[:, i])
+            assert relmax(out['up'][i], up) < TOL64
+            assert relmax(out['down'][i], dn) < TOL64
+            assert relmax(out['net'][i], net) < TOL64
+            assert heating_ok(out['heating'][i], heat, up, dn, c['band_delta'], c['P'], TOL64)
+        # the resident-tau source with the tau of column 0 for every column
+        tau0 = orc.optical_depth(P, T_tau[0], nu, tabs, list(q[:, 0]))
+        res = plan.flux(T, T_g, tau=tau0, albedo=albedo, outputs=('net',))['net']
+        up, dn = orc.get_flux(P, T[-1], T_g[-1], tau0, nu, bands, albedo=albedo[-1])
+        assert relmax(res[-1], orc.net_flux(up, dn, bands['delta'])) < TOL64
