@@ -5,3 +5,4 @@
 #include "flux.cu"
 #include "transmission.cu"
 #include "peaks.cu"
+#include "lines.cu"

@@ -100,6 +100,19 @@ int cmb200_dtransmission_dq_host(const double *tau, int64_t n_lev, int64_t n_nu,
                                  double delta, const double *k_band, const double *scale,
                                  double g, double *out);
 
+/* ---- f3  line-by-line table builder --------------------------------------------------------- */
+/* get_absorption_coefficient (real_gas_data/hitran.py:223-247): Lorentz lines summed onto the
+ * grid nu[n_nu] (evenly spaced) for the levels (p[i], T[i]), i < n_p.  Line l has centre
+ * line_nu (cm^-1), strength line_sw at T_reference (already in m^2/kg units, s_conversion :122),
+ * air-broadened half-width line_gamma_air at (p_reference, T_reference) and temperature exponent
+ * line_n_air; each line is kept within n_line_widths of its widest half-width
+ * (wavenumbers_near_line :182-199).  k[n_p][n_nu] in m^2/kg. */
+int cmb200_line_absorption_host(const cmb200_constants *c, double p_reference, double T_reference,
+                                int64_t n_p, const double *p, const double *T, int64_t n_nu,
+                                const double *nu, int64_t n_lines, const double *line_nu,
+                                const double *line_sw, const double *line_gamma_air,
+                                const double *line_n_air, double n_line_widths, double *k);
+
 /* ---- plan: grids, bands and tables resident on one device ---------------------------------- */
 /* Replaces the state RealGas.__init__ builds (real_gas.py:275-292): interface pressures
  * P[L] ascending, wavenumber grid nu[N] (get_wavenumber_array :300), bands
