@@ -68,6 +68,12 @@ SIGNATURES = {
     'cmb200_line_absorption_host': (C.c_int, [C.POINTER(Constants), C.c_double, C.c_double, C.c_int64, c_double_p,
                                               c_double_p, C.c_int64, c_double_p, C.c_int64, c_double_p, c_double_p,
                                               c_double_p, c_double_p, C.c_double, c_double_p]),
+    'cmb200_stepper_create': (C.c_int, [C.POINTER(C.c_void_p), C.c_void_p, C.c_int64, C.c_double, C.c_double]),
+    'cmb200_stepper_reset': (C.c_int, [C.c_void_p]),
+    'cmb200_stepper_destroy': (C.c_int, [C.c_void_p]),
+    'cmb200_stepper_update': (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double,
+                                        C.c_double, C.c_int, C.c_void_p]),
+    'cmb200_stepper_state': (C.c_int, [C.c_void_p, c_double_p, c_double_p, c_int32_p, c_int32_p]),
     'cmb200_plan_create': (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.POINTER(Constants), C.c_int32,
                                      c_double_p, C.c_int64, c_double_p, C.c_int32, c_int32_p, c_int32_p,
                                      c_double_p, c_double_p, c_uint8_p]),

@@ -6,3 +6,4 @@
 #include "transmission.cu"
 #include "peaks.cu"
 #include "lines.cu"
+#include "stepper.cu"

@@ -1,0 +1,71 @@
+"""Many independent columns stepped on the device: the flux evaluation and the adaptive time
+step of ``Atmosphere.update_temp`` (base.py:166-246, without convective adjustment) run back to
+back on the GPU, every column with its own dt, without a host round trip per step -- the batched
+form of ``RealGas.take_time_step`` (BASELINE configs[2]).
+
+    cols = ColumnStepper(plan, T, T_g, q=q, T_tau=T_tau, albedo=albedo)     # torch CUDA tensors
+    for _ in range(n):
+        delta_net_flux = cols.step()
+    cols.T, cols.t                                                          # [n_col, L-1], [n_col]
+"""
+import ctypes as C
+
+import numpy as np
+
+from .. import _lib
+from .._lib import check
+
+
+class ColumnStepper:
+    def __init__(self, plan, T, T_g, q=None, T_tau=None, tau=None, tau_id=None, albedo=0.3, temp_change=1,
+                 delta_temp_change=0.01):
+        """plan: FluxPlan; T [n_col, L-1], T_g [n_col] and the optical-depth source (q, T_tau or
+        tau, tau_id) as for ``FluxPlan.flux_device`` (torch float64 CUDA tensors).  T is advanced in
+        place.  Level index 0 is the top of the atmosphere, as in ``FluxPlan``."""
+        import torch
+        self.plan, self.T, self.T_g = plan, T, T_g
+        self.source = dict(q=q, T_tau=T_tau, tau=tau, tau_id=tau_id, albedo=albedo)
+        self.n_col = T.shape[0]
+        self.t = torch.zeros(self.n_col, dtype=torch.float64, device=T.device)
+        self.delta_net_flux = torch.empty(self.n_col, dtype=torch.float64, device=T.device)
+        self.out = {}
+        self._lib = _lib.load()
+        self._h = C.c_void_p()
+        check(self._lib.cmb200_stepper_create(C.byref(self._h), plan._h, self.n_col, float(temp_change),
+                                              float(delta_temp_change)))
+
+    def __del__(self):
+        if getattr(self, '_h', None) is not None and self._h.value:
+            self._lib.cmb200_stepper_destroy(self._h)
+            self._h = None
+
+    def reset(self):
+        """Back to t = 0 with the initial time-step state (T is left as it is)."""
+        check(self._lib.cmb200_stepper_reset(self._h))
+        self.t.zero_()
+
+    def step(self, changing_tau=False, net_flux_thresh=1e-7, net_flux_percentile=95):
+        """One adaptive step of every column; returns delta_net_flux [n_col] (device tensor)."""
+        import torch
+        self.out = self.plan.flux_device(self.T, self.T_g, outputs=('net',), out=self.out, **self.source)
+        stream = torch.cuda.current_stream(self.T.device).cuda_stream
+        check(self._lib.cmb200_stepper_update(self._h, self.out['net'].data_ptr(), self.T.data_ptr(), self.t.data_ptr(),
+                                              self.delta_net_flux.data_ptr(), float(net_flux_thresh),
+                                              float(net_flux_percentile), int(bool(changing_tau)),
+                                              C.c_void_p(stream)))
+        return self.delta_net_flux
+
+    @property
+    def net_flux(self):
+        return self.out.get('net')
+
+    def state(self):
+        """Host copies of the per-column time-step state: DeltaT, dt, MaxTendInd (levels counted from
+        the surface like the reference), number of frozen levels."""
+        n = self.n_col
+        dT, dt = np.zeros(n), np.zeros(n)
+        ind, rem = np.zeros(n, dtype=np.int32), np.zeros(n, dtype=np.int32)
+        check(self._lib.cmb200_stepper_state(self._h, _lib.dptr(dT), _lib.dptr(dt),
+                                             ind.ctypes.data_as(C.POINTER(C.c_int32)),
+                                             rem.ctypes.data_as(C.POINTER(C.c_int32))))
+        return {'DeltaT': dT, 'dt': dt, 'MaxTendInd': ind, 'n_removed': rem}

@@ -114,6 +114,8 @@ int cmb200_line_absorption_host(const cmb200_constants *c, double p_reference, d
                                 const double *line_n_air, double n_line_widths, double *k);
 
 /* ---- plan: grids, bands and tables resident on one device ---------------------------------- */
+typedef struct cmb200_stepper cmb200_stepper;
+
 /* Replaces the state RealGas.__init__ builds (real_gas.py:275-292): interface pressures
  * P[L] ascending, wavenumber grid nu[N] (get_wavenumber_array :300), bands
  * (get_wavenumber_bands :336-388) as bin runs band_start/len[B] with centre, delta, sw flag. */
@@ -178,6 +180,27 @@ int cmb200_flux_host(cmb200_plan *plan, const cmb200_flux_io *io);
 int cmb200_flux_workspace_bytes(cmb200_plan *plan, int64_t n_col, int64_t *bytes);
 /* Number of kernel launches issued by this library since load (bench.py's gpu_launches). */
 int64_t cmb200_launch_count(void);
+
+/* ---- f1  adaptive time step, batched over columns on the device ----------------------------- */
+/* Per-column state of Atmosphere.time_step_info (base.py:137-141: DeltaT, MaxTend, MaxTendInd,
+ * nSameMaxInd, nSameMaxInd2, RemoveInd, dt) and the previous net flux, for n_col columns on the
+ * plan's device.  temp_change / delta_temp_change as in Atmosphere.__init__ (base.py:113). */
+int cmb200_stepper_create(cmb200_stepper **stepper, cmb200_plan *plan, int64_t n_col,
+                          double temp_change, double delta_temp_change);
+int cmb200_stepper_reset(cmb200_stepper *stepper);
+int cmb200_stepper_destroy(cmb200_stepper *stepper);
+/* Atmosphere.update_temp with convective_adjust=False (base.py:166-196) and update_time_step
+ * (base.py:197-246) for every column at once.  DEVICE pointers: net[n_col][L] from cmb200_flux,
+ * T[n_col][L-1] updated in place, t[n_col] (seconds) advanced by each column's own dt,
+ * delta_net_flux[n_col] (may be NULL) = percentile of |net - previous net|, 1e6 on a column's
+ * first step or when changing_tau is set.  Runs on `stream`, no synchronisation. */
+int cmb200_stepper_update(cmb200_stepper *stepper, const double *net, double *T, double *t,
+                          double *delta_net_flux, double net_flux_thresh,
+                          double net_flux_percentile, int changing_tau, void *stream);
+/* Copies of the per-column state to HOST arrays of n_col entries (any may be NULL);
+ * max_tend_ind counts levels from the surface like the reference. */
+int cmb200_stepper_state(const cmb200_stepper *stepper, double *delta_T, double *dt,
+                         int32_t *max_tend_ind, int32_t *n_removed);
 
 /* ---- measurement helpers -------------------------------------------------------------------- */
 /* Issue-rate microbenchmarks on the plan-independent current device: dependent-chain-free

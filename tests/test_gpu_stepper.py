@@ -1,0 +1,91 @@
+"""GPU: the batched device-side time step (cmb200_stepper_update) against the host-side
+``Atmosphere.update_temp`` -- itself replayed against the unmodified reference in
+tests/test_host_stepper.py -- fed with the same net fluxes: temperatures, times, dt, DeltaT, the
+level that sets the step, frozen levels and delta_net_flux must be EQUAL, column by column."""
+import numpy as np
+import pytest
+
+from util import load_case
+
+pytestmark = pytest.mark.gpu
+
+
+def host_columns(P_ref, T0):
+    """One reference-orientation (surface first) Atmosphere per column."""
+    from climatemodel_b200.radiation import base
+    cols = []
+    for T in T0:
+        atm = base.Atmosphere(P_ref.size, 1, 1367.0 / 4)
+        atm.p_interface = P_ref.reshape(-1, 1)
+        atm.p = 0.5 * (atm.p_interface[:-1] + atm.p_interface[1:])
+        atm.T = T[::-1].reshape(-1, 1).copy()
+        atm.net_flux = np.zeros((P_ref.size, 1))
+        cols.append(atm)
+    return cols
+
+
+@pytest.mark.parametrize('name,n_steps,temp_change', [('co2_nz50_earth', 40, 1.0), ('co2_nz50_earth', 150, 12.0), ('two_mol_nz41', 60, 6.0)])
+def test_device_steps_equal_host_steps(name, n_steps, temp_change):
+    import torch
+    from climatemodel_b200.plan import FluxPlan
+    from climatemodel_b200.radiation.columns import ColumnStepper
+    c = load_case(name)
+    order = np.argsort(c['P'])
+    P = c['P'][order]
+    L = P.size
+    plan = FluxPlan(P, c['nu'], c['bands'], tables=c['tables'])
+    rng = np.random.default_rng(4)
+    n_col = 6
+    T_base = c['T'][np.argsort(c['p'])]
+    T0 = T_base + rng.normal(0, 4, (n_col, L - 1))
+    T0[1] = 250.0                                                     # an isothermal column
+    T_g = c['T_g'] + rng.normal(0, 3, n_col)
+    q = np.ascontiguousarray(c['q'][:, order])
+    dev = torch.device('cuda', 0)
+    T = torch.tensor(T0, device=dev)
+    cols = ColumnStepper(plan, T, torch.tensor(T_g, device=dev), q=torch.tensor(q, device=dev), albedo=0.3,
+                         temp_change=temp_change)
+    host = host_columns(P[::-1].copy(), T0)
+    for atm in host:
+        atm.time_step_info.update(DeltaT=temp_change, MaxDeltaT=temp_change)
+    t_host = np.zeros(n_col)
+    seen_shrink = seen_removed = False
+    for step in range(n_steps):
+        dnf = cols.step().cpu().numpy()
+        net = cols.net_flux.cpu().numpy()
+        T_dev, t_dev, st = cols.T.cpu().numpy(), cols.t.cpu().numpy(), cols.state()
+        for i, atm in enumerate(host):
+            t_host[i], dnf_host = atm.update_temp(t_host[i], net[i][::-1].reshape(-1, 1).copy())
+            info = atm.time_step_info
+            assert np.array_equal(atm.T[::-1, 0], T_dev[i]), (step, i)
+            assert t_host[i] == t_dev[i] and info['dt'] == st['dt'][i], (step, i)
+            assert info['DeltaT'] == st['DeltaT'][i] and info['MaxTendInd'] == st['MaxTendInd'][i], (step, i)
+            assert len(info['RemoveInd']) == st['n_removed'][i], (step, i)
+            assert dnf_host == dnf[i], (step, i)
+            seen_shrink |= info['DeltaT'] < temp_change
+            seen_removed |= len(info['RemoveInd']) > 0
+    if temp_change > 1:
+        assert seen_shrink                     # the oscillation branch was exercised
+    assert np.all(t_dev > 0) and len(set(np.round(t_dev, 3))) > 1     # every column on its own clock
+
+
+def test_changing_tau_and_reset():
+    import torch
+    from climatemodel_b200.plan import FluxPlan
+    from climatemodel_b200.radiation.columns import ColumnStepper
+    c = load_case('co2_nz50_earth')
+    order = np.argsort(c['P'])
+    P = c['P'][order]
+    plan = FluxPlan(P, c['nu'], c['bands'], tables=c['tables'])
+    dev = torch.device('cuda', 0)
+    T0 = np.tile(c['T'][np.argsort(c['p'])], (3, 1))
+    T = torch.tensor(T0, device=dev)
+    cols = ColumnStepper(plan, T, torch.full((3,), c['T_g'], device=dev, dtype=torch.float64),
+                         q=torch.tensor(np.ascontiguousarray(c['q'][:, order]), device=dev))
+    assert np.all(cols.step().cpu().numpy() == 1e6)                   # first step: no previous net flux
+    assert np.all(cols.step().cpu().numpy() < 1e6)
+    assert np.all(cols.step(changing_tau=True).cpu().numpy() == 1e6)
+    t3 = cols.t.cpu().numpy().copy()
+    assert np.all(t3 > 0) and np.all(t3 == t3[0])                     # identical columns stay identical
+    cols.reset()
+    assert np.all(cols.t.cpu().numpy() == 0) and np.all(cols.state()['MaxTendInd'] == -1)
