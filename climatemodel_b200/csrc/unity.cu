@@ -7,3 +7,4 @@
 #include "peaks.cu"
 #include "lines.cu"
 #include "stepper.cu"
+#include "grey.cu"

@@ -202,6 +202,19 @@ int cmb200_stepper_update(cmb200_stepper *stepper, const double *net, double *T,
 int cmb200_stepper_state(const cmb200_stepper *stepper, double *delta_T, double *dt,
                          int32_t *max_tend_ind, int32_t *n_removed);
 
+/* ---- grey two-stream fluxes (the reference's other radiation scheme) ------------------------- */
+/* GreyGas.get_lw_flux (grey.py:251-275) and get_sw_flux (:277-294) for ny columns at once.
+ * HOST arrays in the reference's layout [level][column], level 0 at the surface:
+ * T, dtau [nz-1][ny]; toa_up_lw[ny] = (1 - albedo_mod) solar_latitude_factor F / 4 (:265);
+ * up_sw0 / down_sw0 [ny] = the short-wave streams without atmosphere (:287-290, may be NULL);
+ * tau_sw [nz][ny] short-wave optical depth on the interfaces (NULL: transparent or
+ * isothermal=True).  Outputs [nz][ny]: up_lw, down_lw, and optionally up_sw, down_sw,
+ * net = up_lw - down_lw + up_sw - down_sw (:341). */
+int cmb200_grey_flux_host(int32_t nz, int64_t ny, double sigma, const double *T, const double *dtau,
+                          const double *toa_up_lw, const double *up_sw0, const double *down_sw0,
+                          const double *tau_sw, double *up_lw, double *down_lw, double *up_sw,
+                          double *down_sw, double *net);
+
 /* ---- measurement helpers -------------------------------------------------------------------- */
 /* Issue-rate microbenchmarks on the plan-independent current device: dependent-chain-free
  * DFMA and FFMA loops (TFLOP/s, 2 flop per FMA) and a device copy (GB/s, read+write). */

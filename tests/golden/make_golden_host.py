@@ -94,5 +94,41 @@ def main():
     np.savez_compressed(os.path.join(HERE, 'host_stepper.npz'), **out)
 
 
+def grey_cases():
+    """``host_grey.npz``: inputs and outputs of the reference grey two-stream fluxes
+    (GreyGas.get_lw_flux / get_sw_flux, grey.py:251-294) for a long-wave-only atmosphere and one
+    with a short-wave absorber, 7 latitudes, perturbed temperatures."""
+    import importlib
+    load_reference()
+    grey = importlib.import_module('Model.radiation.grey')
+    god = importlib.import_module('Model.radiation.grey_optical_depth')
+    out = {}
+    rng = np.random.default_rng(5)
+    p_s = 101320.0
+    for tag, sw in [('lw', None), ('sw', god.exponential)]:
+        gas = grey.GreyGas(nz=36, ny=7, tau_lw_func=god.scale_height, tau_lw_func_args=[0.22 * p_s, 4, p_s],
+                           tau_sw_func=sw, tau_sw_func_args=None if sw is None else [0.3 * p_s, 0.4, p_s],
+                           albedo=np.linspace(0.2, 0.5, 7))
+        gas.T = gas.T + rng.normal(0, 12, gas.T.shape)
+        gas.get_lw_flux()
+        up_sw, down_sw = gas.get_sw_flux()
+        iso = gas.get_sw_flux(isothermal=True)
+        net = gas.up_lw_flux - gas.down_lw_flux + up_sw - down_sw
+        out.update({tag + '_T': gas.T.copy(), tag + '_dtau': gas.dtau.copy(), tag + '_F_sw0': np.asarray((1 - gas.albedo_mod) * gas.solar_latitude_factor * gas.F_stellar_constant / 4),
+                    tag + '_albedo_mod': np.asarray(gas.albedo_mod, dtype=float) * np.ones(7),
+                    tag + '_solar_factor': np.asarray(gas.solar_latitude_factor, dtype=float) * np.ones(7),
+                    tag + '_F_stellar': float(gas.F_stellar_constant),
+                    tag + '_tau_sw_interface': np.zeros_like(gas.tau_interface) if sw is None else gas.tau_sw_interface.copy(),
+                    tag + '_up_lw': gas.up_lw_flux.copy(), tag + '_down_lw': gas.down_lw_flux.copy(),
+                    tag + '_up_sw': up_sw.copy(), tag + '_down_sw': down_sw.copy(), tag + '_net': net.copy(),
+                    tag + '_up_sw_iso': iso[0].copy(), tag + '_down_sw_iso': iso[1].copy()})
+    np.savez_compressed(os.path.join(HERE, 'host_grey.npz'), **out)
+    print('grey', {k: np.shape(v) for k, v in out.items() if k.startswith('sw_')})
+
+
 if __name__ == '__main__':
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == 'grey':
+        grey_cases()
+    else:
+        main()
+        grey_cases()
