@@ -251,7 +251,9 @@ def run_b200(a):
     # ---- end to end through the host-buffer C ABI -----------------------------------------------------
     e2e = None
     if not a.no_e2e:
-        args = dict(T_tau=hTt.numpy(), q=hq.numpy(), albedo=hal.numpy(), outputs=('net', 'heating'))
+        h_out = {'net': torch.empty((n_col, L), dtype=torch.float64, pin_memory=True).numpy(),
+                 'heating': torch.empty((n_col, L - 1), dtype=torch.float64, pin_memory=True).numpy()}
+        args = dict(T_tau=hTt.numpy(), q=hq.numpy(), albedo=hal.numpy(), outputs=('net', 'heating'), out=h_out)
         plan.flux(hT.numpy(), hTg.numpy(), **args)
         barrier()
         t0 = time.perf_counter()

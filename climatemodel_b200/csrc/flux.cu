@@ -43,13 +43,13 @@ static double cost_knob(const char *name, double dflt) {
 // of segments of equal estimated cost, and one partial-sum slot per (part, band) run.
 static int ensure_partition(cmb200_plan *p, int64_t n_col, int W, int resident_ctas) {
     Partition &pt = p->partition;
-    if (pt.n_col == n_col && pt.warps == W) return CMB200_OK;
     int C = 1;
     if (n_col < resident_ctas) {
         const int64_t want = (resident_ctas + n_col - 1) / n_col;
         const int64_t most = std::max<int64_t>(1, p->n_seg / (2 * W));   // keep two segments per warp
         C = (int)std::max<int64_t>(1, std::min(want, most));
     }
+    if (pt.n_col >= 0 && pt.warps == W && pt.ctas_per_col == C) return CMB200_OK;   // same decomposition
     const int parts = C * W, n_seg = p->n_seg;
     const double kCostLW = cost_knob("CMB200_COST_LW", 1.5), kCostRun = cost_knob("CMB200_COST_RUN", 0.4);
     std::vector<double> prefix(n_seg + 1, 0.0);
@@ -398,6 +398,33 @@ extern "C" int cmb200_flux(cmb200_plan *plan, const cmb200_flux_io *io, void *st
     return CMB200_ERR_LIMIT;
 }
 
+// Host-pointer entry point: columns are streamed through the device in chunks, with the copy of
+// the next chunk's inputs and of the previous chunk's outputs overlapping the kernels of the
+// current one (three streams, double-buffered staging kept on the plan between calls).  The
+// kernels of successive chunks run in order on one stream because they share the plan's scratch.
+struct cmb200_host_pipe {
+    cudaStream_t h2d = nullptr, comp = nullptr, d2h = nullptr;
+    cudaEvent_t in_ready[2] = {nullptr, nullptr}, computed[2] = {nullptr, nullptr}, out_done[2] = {nullptr, nullptr};
+    cmb::DevBuf<double> T[2], Tg[2], alb[2], Ttau[2], q[2], up[2], down[2], net[2], heat[2], Tint[2], tau;
+    cmb::DevBuf<int32_t> tid[2];
+    ~cmb200_host_pipe() {
+        for (int b = 0; b < 2; ++b) {
+            if (in_ready[b]) cudaEventDestroy(in_ready[b]);
+            if (computed[b]) cudaEventDestroy(computed[b]);
+            if (out_done[b]) cudaEventDestroy(out_done[b]);
+        }
+        if (h2d) cudaStreamDestroy(h2d);
+        if (comp) cudaStreamDestroy(comp);
+        if (d2h) cudaStreamDestroy(d2h);
+    }
+};
+void cmb::destroy_host_pipe(cmb200_host_pipe *p) { delete p; }
+
+template <typename T>
+static cudaError_t grow(cmb::DevBuf<T> &b, size_t n) {
+    return b.n >= n ? cudaSuccess : b.alloc(n);
+}
+
 extern "C" int cmb200_flux_host(cmb200_plan *plan, const cmb200_flux_io *io) {
     int rc = validate_flux_io(plan, io);
     if (rc) return rc;
@@ -405,64 +432,120 @@ extern "C" int cmb200_flux_host(cmb200_plan *plan, const cmb200_flux_io *io) {
     CMB_CUDA(cudaSetDevice(plan->device));
     const int64_t n = io->n_col;
     const int L = plan->L, B = plan->B, M = plan->M;
-    cmb200_flux_io d = *io;
-    DevBuf<double> T, Tg, alb, tau, Ttau, q, up, down, net, heat, Tint;
-    DevBuf<int32_t> tid;
-    CMB_CUDA(T.upload(io->T, (size_t)n * (L - 1)));
-    d.T = T.p;
-    CMB_CUDA(Tg.upload(io->T_g, n));
-    d.T_g = Tg.p;
-    if (io->albedo) {
-        CMB_CUDA(alb.upload(io->albedo, n));
-        d.albedo = alb.p;
+    if (io->tau && io->tau_id)
+        for (int64_t i = 0; i < n; ++i)
+            CMB_CHECK_ARG(io->tau_id[i] >= 0 && io->tau_id[i] < io->n_tau, "tau_id[%lld] out of range", (long long)i);
+    if (!plan->host_pipe) {
+        cmb200_host_pipe *hp = new cmb200_host_pipe();
+        plan->host_pipe = hp;
+        CMB_CUDA(cudaStreamCreateWithFlags(&hp->h2d, cudaStreamNonBlocking));
+        CMB_CUDA(cudaStreamCreateWithFlags(&hp->comp, cudaStreamNonBlocking));
+        CMB_CUDA(cudaStreamCreateWithFlags(&hp->d2h, cudaStreamNonBlocking));
+        for (int b = 0; b < 2; ++b) {
+            CMB_CUDA(cudaEventCreateWithFlags(&hp->in_ready[b], cudaEventDisableTiming));
+            CMB_CUDA(cudaEventCreateWithFlags(&hp->computed[b], cudaEventDisableTiming));
+            CMB_CUDA(cudaEventCreateWithFlags(&hp->out_done[b], cudaEventDisableTiming));
+        }
     }
+    cmb200_host_pipe &hp = *plan->host_pipe;
+    // chunk: a multiple of the resident CTA count, ~16 chunks for large batches, one for small ones
+    const int64_t quantum = (int64_t)sm_count(plan->device) * 8;
+    int64_t chunk = n;
+    if (n > 4 * quantum) chunk = std::min<int64_t>(std::max<int64_t>(((n / 16 + quantum - 1) / quantum) * quantum, 4 * quantum), 64 * quantum);
+    const bool fused = io->tau == nullptr, q_cols = fused && io->q_per_column;
+    const int n_buf = chunk < n ? 2 : 1;
+    for (int b = 0; b < n_buf; ++b) {
+        CMB_CUDA(grow(hp.T[b], (size_t)chunk * (L - 1)));
+        CMB_CUDA(grow(hp.Tg[b], (size_t)chunk));
+        if (io->albedo) CMB_CUDA(grow(hp.alb[b], (size_t)chunk));
+        if (io->tau && io->tau_id) CMB_CUDA(grow(hp.tid[b], (size_t)chunk));
+        if (fused && io->T_tau) CMB_CUDA(grow(hp.Ttau[b], (size_t)chunk * L));
+        if (q_cols) CMB_CUDA(grow(hp.q[b], (size_t)M * chunk * L));
+        if (io->up) CMB_CUDA(grow(hp.up[b], (size_t)chunk * L * B));
+        if (io->down) CMB_CUDA(grow(hp.down[b], (size_t)chunk * L * B));
+        if (io->net) CMB_CUDA(grow(hp.net[b], (size_t)chunk * L));
+        if (io->heating) CMB_CUDA(grow(hp.heat[b], (size_t)chunk * (L - 1)));
+        if (io->T_interface) CMB_CUDA(grow(hp.Tint[b], (size_t)chunk * L));
+    }
+    // column-independent inputs: once, ahead of the first chunk
     if (io->tau) {
-        CMB_CUDA(tau.upload(io->tau, (size_t)io->n_tau * L * plan->N));
-        d.tau = tau.p;
-        if (io->tau_id) {
-            for (int64_t i = 0; i < n; ++i)
-                CMB_CHECK_ARG(io->tau_id[i] >= 0 && io->tau_id[i] < io->n_tau, "tau_id[%lld] out of range", (long long)i);
-            CMB_CUDA(tid.upload(io->tau_id, n));
-            d.tau_id = tid.p;
+        CMB_CUDA(grow(hp.tau, (size_t)io->n_tau * L * plan->N));
+        CMB_CUDA(cudaMemcpyAsync(hp.tau.p, io->tau, (size_t)io->n_tau * L * plan->N * sizeof(double), cudaMemcpyHostToDevice, hp.h2d));
+    } else if (!q_cols) {
+        CMB_CUDA(grow(hp.q[0], (size_t)M * L));
+        CMB_CUDA(cudaMemcpyAsync(hp.q[0].p, io->q, (size_t)M * L * sizeof(double), cudaMemcpyHostToDevice, hp.h2d));
+    }
+    auto h2d = [&](double *dst, const double *src, size_t count) {
+        return cudaMemcpyAsync(dst, src, count * sizeof(double), cudaMemcpyHostToDevice, hp.h2d);
+    };
+    auto d2h = [&](double *dst, const double *src, size_t count) {
+        return cudaMemcpyAsync(dst, src, count * sizeof(double), cudaMemcpyDeviceToHost, hp.d2h);
+    };
+    // Host order is software-pipelined too: chunk k's inputs and kernels are queued before chunk
+    // k-1's outputs are fetched, so a copy that blocks the host (pageable memory) does not starve
+    // the device.
+    const int64_t n_chunks = (n + chunk - 1) / chunk;
+    auto fetch_outputs = [&](int64_t k) -> int {
+        const int b = (int)(k % n_buf);
+        const int64_t c0 = k * chunk, m = std::min(chunk, n - c0);
+        // ---- outputs ------------------------------------------------------------------------------------
+        CMB_CUDA(cudaStreamWaitEvent(hp.d2h, hp.computed[b], 0));
+        if (io->up) CMB_CUDA(d2h(io->up + c0 * L * B, hp.up[b].p, (size_t)m * L * B));
+        if (io->down) CMB_CUDA(d2h(io->down + c0 * L * B, hp.down[b].p, (size_t)m * L * B));
+        if (io->net) CMB_CUDA(d2h(io->net + c0 * L, hp.net[b].p, (size_t)m * L));
+        if (io->heating) CMB_CUDA(d2h(io->heating + c0 * (L - 1), hp.heat[b].p, (size_t)m * (L - 1)));
+        if (io->T_interface) CMB_CUDA(d2h(io->T_interface + c0 * L, hp.Tint[b].p, (size_t)m * L));
+        CMB_CUDA(cudaEventRecord(hp.out_done[b], hp.d2h));
+        return CMB200_OK;
+    };
+    for (int64_t k = 0; k < n_chunks; ++k) {
+        const int64_t c0 = k * chunk;
+        const int b = (int)(k % n_buf);
+        const int64_t m = std::min(chunk, n - c0);
+        // ---- inputs of this chunk (the buffer's previous kernels must be done with them) ----------
+        if (k >= n_buf) CMB_CUDA(cudaStreamWaitEvent(hp.h2d, hp.computed[b], 0));
+        CMB_CUDA(h2d(hp.T[b].p, io->T + c0 * (L - 1), (size_t)m * (L - 1)));
+        CMB_CUDA(h2d(hp.Tg[b].p, io->T_g + c0, (size_t)m));
+        if (io->albedo) CMB_CUDA(h2d(hp.alb[b].p, io->albedo + c0, (size_t)m));
+        if (io->tau && io->tau_id)
+            CMB_CUDA(cudaMemcpyAsync(hp.tid[b].p, io->tau_id + c0, (size_t)m * sizeof(int32_t), cudaMemcpyHostToDevice, hp.h2d));
+        if (fused && io->T_tau) CMB_CUDA(h2d(hp.Ttau[b].p, io->T_tau + c0 * L, (size_t)m * L));
+        if (q_cols)
+            for (int mol = 0; mol < M; ++mol)
+                CMB_CUDA(h2d(hp.q[b].p + (size_t)mol * m * L, io->q + ((size_t)mol * n + c0) * L, (size_t)m * L));
+        CMB_CUDA(cudaEventRecord(hp.in_ready[b], hp.h2d));
+        // ---- kernels ------------------------------------------------------------------------------------
+        cmb200_flux_io d = *io;
+        d.n_col = m;
+        d.T = hp.T[b].p;
+        d.T_g = hp.Tg[b].p;
+        d.albedo = io->albedo ? hp.alb[b].p : nullptr;
+        d.tau = io->tau ? hp.tau.p : nullptr;
+        d.tau_id = io->tau && io->tau_id ? hp.tid[b].p : nullptr;
+        d.T_tau = fused && io->T_tau ? hp.Ttau[b].p : nullptr;
+        d.q = fused ? (q_cols ? hp.q[b].p : hp.q[0].p) : nullptr;
+        d.up = io->up ? hp.up[b].p : nullptr;
+        d.down = io->down ? hp.down[b].p : nullptr;
+        d.net = io->net ? hp.net[b].p : nullptr;
+        d.heating = io->heating ? hp.heat[b].p : nullptr;
+        d.T_interface = io->T_interface ? hp.Tint[b].p : nullptr;
+        CMB_CUDA(cudaStreamWaitEvent(hp.comp, hp.in_ready[b], 0));
+        if (k >= n_buf) CMB_CUDA(cudaStreamWaitEvent(hp.comp, hp.out_done[b], 0));   // outputs of chunk k-2 copied out
+        // bands outside the plan's band / segment range are not written by the kernels: they read as zero
+        if (d.up) CMB_CUDA(cudaMemsetAsync(d.up, 0, (size_t)m * L * B * sizeof(double), hp.comp));
+        if (d.down) CMB_CUDA(cudaMemsetAsync(d.down, 0, (size_t)m * L * B * sizeof(double), hp.comp));
+        rc = cmb200_flux(plan, &d, hp.comp);
+        if (rc) {
+            cudaDeviceSynchronize();
+            return rc;
         }
-    } else {
-        if (io->T_tau) {
-            CMB_CUDA(Ttau.upload(io->T_tau, (size_t)n * L));
-            d.T_tau = Ttau.p;
-        }
-        CMB_CUDA(q.upload(io->q, (size_t)M * (io->q_per_column ? n : 1) * L));
-        d.q = q.p;
+        CMB_CUDA(cudaEventRecord(hp.computed[b], hp.comp));
+        if (k >= 1 && (rc = fetch_outputs(k - 1))) return rc;
     }
-    if (io->up) {
-        CMB_CUDA(up.alloc((size_t)n * L * B));
-        CMB_CUDA(cudaMemsetAsync(up.p, 0, up.n * sizeof(double)));
-        d.up = up.p;
-    }
-    if (io->down) {
-        CMB_CUDA(down.alloc((size_t)n * L * B));
-        CMB_CUDA(cudaMemsetAsync(down.p, 0, down.n * sizeof(double)));
-        d.down = down.p;
-    }
-    if (io->net) {
-        CMB_CUDA(net.alloc((size_t)n * L));
-        d.net = net.p;
-    }
-    if (io->heating) {
-        CMB_CUDA(heat.alloc((size_t)n * (L - 1)));
-        d.heating = heat.p;
-    }
-    if (io->T_interface) {
-        CMB_CUDA(Tint.alloc((size_t)n * L));
-        d.T_interface = Tint.p;
-    }
-    rc = cmb200_flux(plan, &d, nullptr);
-    if (rc) return rc;
-    if (io->up) CMB_CUDA(cudaMemcpyAsync(io->up, up.p, up.n * sizeof(double), cudaMemcpyDeviceToHost));
-    if (io->down) CMB_CUDA(cudaMemcpyAsync(io->down, down.p, down.n * sizeof(double), cudaMemcpyDeviceToHost));
-    if (io->net) CMB_CUDA(cudaMemcpyAsync(io->net, net.p, net.n * sizeof(double), cudaMemcpyDeviceToHost));
-    if (io->heating) CMB_CUDA(cudaMemcpyAsync(io->heating, heat.p, heat.n * sizeof(double), cudaMemcpyDeviceToHost));
-    if (io->T_interface) CMB_CUDA(cudaMemcpyAsync(io->T_interface, Tint.p, Tint.n * sizeof(double), cudaMemcpyDeviceToHost));
-    CMB_CUDA(cudaDeviceSynchronize());
+    if ((rc = fetch_outputs(n_chunks - 1))) return rc;
+    CMB_CUDA(cudaStreamSynchronize(hp.h2d));
+    CMB_CUDA(cudaStreamSynchronize(hp.comp));
+    CMB_CUDA(cudaStreamSynchronize(hp.d2h));
     return CMB200_OK;
 }
 

@@ -27,6 +27,11 @@ struct Partition {
 
 }  // namespace cmb
 
+struct cmb200_host_pipe;
+namespace cmb {
+void destroy_host_pipe(cmb200_host_pipe *p);
+}
+
 struct cmb200_plan {
     int device = 0;
     int precision = CMB200_F64;
@@ -69,6 +74,10 @@ struct cmb200_plan {
     cmb::DevBuf<double> Tint, scratch, coefbuf;
     cmb::DevBuf<uint8_t> tidx;
     cmb::DevBuf<unsigned long long> task_counter;
+    cmb200_host_pipe *host_pipe = nullptr;   // streams and staging buffers of cmb200_flux_host
+    ~cmb200_plan() {
+        if (host_pipe) cmb::destroy_host_pipe(host_pipe);
+    }
 };
 
 namespace cmb {

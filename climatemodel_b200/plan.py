@@ -143,14 +143,15 @@ class FluxPlan:
 
     # -- host (NumPy) path ------------------------------------------------------------------
     def flux(self, T, T_g, tau=None, tau_id=None, T_tau=None, q=None, albedo=0.3,
-             outputs=('up', 'down', 'net', 'heating')):
+             outputs=('up', 'down', 'net', 'heating'), out=None):
         """Fluxes for n_col columns.  T [n_col, L-1] (or [L-1]), T_g [n_col] (or scalar).
 
         Optical-depth source: ``tau`` [L, N] or [n_tau, L, N] (+ ``tau_id`` [n_col]) -- or, when
         ``tau`` is None, the plan's tables with lookup temperatures ``T_tau`` [n_col, L] (None:
         isothermal at T_g) and specific humidities ``q`` [M, L] or [M, n_col, L].
         Returns a dict of NumPy arrays: up/down [n_col, L, B], net [n_col, L],
-        heating [n_col, L-1], T_interface [n_col, L] -- as requested in ``outputs``."""
+        heating [n_col, L-1], T_interface [n_col, L] -- as requested in ``outputs``; arrays given in
+        ``out`` (e.g. page-locked ones, so that the copies overlap the kernels) are filled in place."""
         L, B = self.L, self.B
         T = as_f64(T)
         if T.ndim == 1:
@@ -170,12 +171,16 @@ class FluxPlan:
             keep.append(a)
             io.albedo = a.ctypes.data
         self._fill_tau_source(io, keep, n_col, tau, tau_id, T_tau, q, host=True)
-        out = {}
+        out = {} if out is None else out
         shapes = {'up': (n_col, L, B), 'down': (n_col, L, B), 'net': (n_col, L),
                   'heating': (n_col, L - 1), 'T_interface': (n_col, L)}
         for name in outputs:
-            out[name] = np.zeros(shapes[name])
-            setattr(io, name, out[name].ctypes.data)
+            if name not in out:
+                out[name] = np.zeros(shapes[name])
+            a = out[name]
+            if a.shape != shapes[name] or a.dtype != np.float64 or not a.flags.c_contiguous:
+                raise ValueError('out[%r] must be a C-contiguous float64 array of shape %s' % (name, shapes[name]))
+            setattr(io, name, a.ctypes.data)
         check(self._lib.cmb200_flux_host(self._h, C.byref(io)))
         return out
 
