@@ -19,6 +19,9 @@ struct cmb200_stepper {
     cmb::DevBuf<double> delta_T, max_tend, dt, prev_net;
     cmb::DevBuf<int32_t> max_tend_ind, n_same, n_same2, n_removed;
     cmb::DevBuf<uint8_t> removed;      // [n_col][L-1], reference level index
+    cmb::DevBuf<uint8_t> active, conv_level;   // layers updated in the last step; layers the last convective adjustment moved
+    cmb::DevBuf<int32_t> conv_status;
+    cmb::DevBuf<double> p_centre, p_power;     // reference order (surface first): p and (p / p_ref)^alpha
     double temp_change = 1.0, delta_temp_change = 0.01;
 };
 
@@ -29,7 +32,10 @@ struct StepperArgs {
     int64_t n_col;
     const double *Pint;
     double g_over_cp, thresh, quantile, max_delta_T, delta_T_step;
-    int changing_tau;
+    int changing_tau, convective;
+    double conv_mult;
+    const uint8_t *conv_level;
+    uint8_t *active;
     const double *net;
     double *T, *t, *dnf;
     double *delta_T, *max_tend, *dt, *prev_net;
@@ -131,6 +137,7 @@ __global__ void stepper_update_kernel(const StepperArgs a) {
         }
         dt = DeltaT / fabs(tnd);
         if (isinf(dt)) dt = 24.0 * 60.0 * 60.0;
+        if (a.convective && a.conv_level[col * nl + best_r]) dt = dt * a.conv_mult;     // base.py:181-184
         a.delta_T[col] = DeltaT;
         a.n_same[col] = n1;
         a.n_same2[col] = n2;
@@ -149,6 +156,7 @@ __global__ void stepper_update_kernel(const StepperArgs a) {
         const bool was_removed_before = removed[r] && r != best_r;
         const bool act = normal ? (fabs(net[k + 1]) > a.thresh && !was_removed_before) : true;
         if (act) T[k] = __dadd_rn(T[k], __dmul_rn(dt, tend[k]));
+        if (a.active) a.active[col * nl + r] = act;
     }
     for (int i = lane; i < L; i += 32) prev[i] = net[i];
     if (lane == 0) {
@@ -192,6 +200,12 @@ extern "C" int cmb200_stepper_reset(cmb200_stepper *s) {
     CMB_CUDA(s->n_removed.upload(izero.data(), n));
     if (s->prev_net.n < n * L) CMB_CUDA(s->prev_net.alloc(n * L));
     if (s->removed.n < n * (L - 1)) CMB_CUDA(s->removed.alloc(n * (L - 1)));
+    if (s->active.n < n * (L - 1)) CMB_CUDA(s->active.alloc(n * (L - 1)));
+    if (s->conv_level.n < n * (L - 1)) CMB_CUDA(s->conv_level.alloc(n * (L - 1)));
+    if (s->conv_status.n < n) CMB_CUDA(s->conv_status.alloc(n));
+    CMB_CUDA(cudaMemset(s->active.p, 0, n * (L - 1)));
+    CMB_CUDA(cudaMemset(s->conv_level.p, 0, n * (L - 1)));
+    CMB_CUDA(cudaMemset(s->conv_status.p, 0, n * sizeof(int32_t)));
     CMB_CUDA(cudaMemset(s->prev_net.p, 0, n * L * sizeof(double)));
     CMB_CUDA(cudaMemset(s->removed.p, 0, n * (L - 1)));
     CMB_CUDA(cudaDeviceSynchronize());
@@ -205,9 +219,9 @@ extern "C" int cmb200_stepper_destroy(cmb200_stepper *s) {
     return CMB200_OK;
 }
 
-extern "C" int cmb200_stepper_update(cmb200_stepper *s, const double *net, double *T, double *t,
-                                     double *delta_net_flux, double net_flux_thresh,
-                                     double net_flux_percentile, int changing_tau, void *stream) {
+static int stepper_update(cmb200_stepper *s, const double *net, double *T, double *t, double *delta_net_flux,
+                          double net_flux_thresh, double net_flux_percentile, int changing_tau, int convective,
+                          double conv_mult, void *stream) {
     CMB_CHECK_ARG(s && net && T && t, "null pointer");
     CMB_CHECK_ARG(net_flux_percentile >= 0 && net_flux_percentile <= 100, "percentile must be within [0, 100]");
     if (s->n_col == 0) return CMB200_OK;
@@ -222,6 +236,10 @@ extern "C" int cmb200_stepper_update(cmb200_stepper *s, const double *net, doubl
     a.max_delta_T = s->temp_change;
     a.delta_T_step = s->delta_temp_change;
     a.changing_tau = changing_tau;
+    a.convective = convective;
+    a.conv_mult = conv_mult;
+    a.conv_level = s->conv_level.p;
+    a.active = s->active.p;
     a.net = net;
     a.T = T;
     a.t = t;
@@ -240,6 +258,40 @@ extern "C" int cmb200_stepper_update(cmb200_stepper *s, const double *net, doubl
     stepper_update_kernel<<<(unsigned)((s->n_col + warps - 1) / warps), warps * 32, smem, (cudaStream_t)stream>>>(a);
     CMB_LAUNCHED();
     return CMB200_OK;
+}
+
+extern "C" int cmb200_stepper_update(cmb200_stepper *s, const double *net, double *T, double *t,
+                                     double *delta_net_flux, double net_flux_thresh,
+                                     double net_flux_percentile, int changing_tau, void *stream) {
+    return stepper_update(s, net, T, t, delta_net_flux, net_flux_thresh, net_flux_percentile, changing_tau, 0, 1.0, stream);
+}
+
+extern "C" int cmb200_stepper_set_convection(cmb200_stepper *s, const double *p_centre, const double *p_power) {
+    CMB_CHECK_ARG(s && p_centre && p_power, "null pointer");
+    CMB_CUDA(cudaSetDevice(s->plan->device));
+    const int nl = s->plan->L - 1;
+    for (int r = 1; r < nl; ++r) CMB_CHECK_ARG(p_centre[r] < p_centre[r - 1], "p_centre must descend (surface first)");
+    CMB_CUDA(s->p_centre.upload(p_centre, nl));
+    CMB_CUDA(s->p_power.upload(p_power, nl));
+    CMB_CUDA(cudaDeviceSynchronize());
+    return CMB200_OK;
+}
+
+extern "C" int cmb200_stepper_update_convective(cmb200_stepper *s, const double *net, double *T, double *t,
+                                                double *delta_net_flux, double net_flux_thresh,
+                                                double net_flux_percentile, int changing_tau, double conv_thresh,
+                                                double conv_t_multiplier, void *stream) {
+    CMB_CHECK_ARG(s, "null pointer");
+    if (s->n_col == 0) return CMB200_OK;
+    if (!s->p_centre.p) {
+        set_error("cmb200_stepper_set_convection has not been called");
+        return CMB200_ERR_STATE;
+    }
+    int rc = stepper_update(s, net, T, t, delta_net_flux, net_flux_thresh, net_flux_percentile, changing_tau, 1,
+                            conv_t_multiplier, stream);
+    if (rc) return rc;
+    return cmb200_convective_adjust(s->plan->L - 1, s->n_col, s->p_centre.p, s->p_power.p, conv_thresh, T,
+                                    s->active.p, s->conv_level.p, s->conv_status.p, stream);
 }
 
 extern "C" int cmb200_stepper_state(const cmb200_stepper *s, double *delta_T, double *dt, int32_t *max_tend_ind,

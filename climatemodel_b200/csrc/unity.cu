@@ -6,5 +6,6 @@
 #include "transmission.cu"
 #include "peaks.cu"
 #include "lines.cu"
+#include "convect.cu"
 #include "stepper.cu"
 #include "grey.cu"

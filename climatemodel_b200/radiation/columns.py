@@ -1,7 +1,8 @@
-"""Many independent columns stepped on the device: the flux evaluation and the adaptive time
-step of ``Atmosphere.update_temp`` (base.py:166-246, without convective adjustment) run back to
-back on the GPU, every column with its own dt, without a host round trip per step -- the batched
-form of ``RealGas.take_time_step`` (BASELINE configs[2]).
+"""Many independent columns stepped on the device: the flux evaluation, the adaptive time step
+of ``Atmosphere.update_temp`` (base.py:166-246) and, optionally, the dry convective adjustment
+(convective_adjustment.py:7-135) run back to back on the GPU, every column with its own dt,
+without a host round trip per step -- the batched form of ``RealGas.take_time_step``
+(BASELINE configs[2]).
 
     cols = ColumnStepper(plan, T, T_g, q=q, T_tau=T_tau, albedo=albedo)     # torch CUDA tensors
     for _ in range(n):
@@ -33,6 +34,13 @@ class ColumnStepper:
         self._h = C.c_void_p()
         check(self._lib.cmb200_stepper_create(C.byref(self._h), plan._h, self.n_col, float(temp_change),
                                               float(delta_temp_change)))
+        # cell centres in the reference's order (surface first) and (p / p_ref)^alpha as NumPy evaluates it
+        from .convective_adjustment import g, c_p_dry, p_surface_earth, R_specific
+        P_ref = np.asarray(plan.P, dtype=float)[::-1]
+        self.p_centre = np.ascontiguousarray((P_ref[:-1] + P_ref[1:]) / 2)
+        alpha = R_specific * (g / c_p_dry) / g
+        self.p_power = np.ascontiguousarray((self.p_centre / p_surface_earth) ** alpha)
+        check(self._lib.cmb200_stepper_set_convection(self._h, _lib.dptr(self.p_centre), _lib.dptr(self.p_power)))
 
     def __del__(self):
         if getattr(self, '_h', None) is not None and self._h.value:
@@ -44,15 +52,21 @@ class ColumnStepper:
         check(self._lib.cmb200_stepper_reset(self._h))
         self.t.zero_()
 
-    def step(self, changing_tau=False, net_flux_thresh=1e-7, net_flux_percentile=95):
-        """One adaptive step of every column; returns delta_net_flux [n_col] (device tensor)."""
+    def step(self, changing_tau=False, convective_adjust=False, net_flux_thresh=1e-7, net_flux_percentile=95,
+             conv_thresh=1e-5, conv_t_multiplier=5):
+        """One adaptive step of every column (arguments as ``Atmosphere.update_temp``); returns
+        delta_net_flux [n_col] (device tensor)."""
         import torch
         self.out = self.plan.flux_device(self.T, self.T_g, outputs=('net',), out=self.out, **self.source)
         stream = torch.cuda.current_stream(self.T.device).cuda_stream
-        check(self._lib.cmb200_stepper_update(self._h, self.out['net'].data_ptr(), self.T.data_ptr(), self.t.data_ptr(),
-                                              self.delta_net_flux.data_ptr(), float(net_flux_thresh),
-                                              float(net_flux_percentile), int(bool(changing_tau)),
-                                              C.c_void_p(stream)))
+        head = (self._h, self.out['net'].data_ptr(), self.T.data_ptr(), self.t.data_ptr(),
+                self.delta_net_flux.data_ptr(), float(net_flux_thresh), float(net_flux_percentile),
+                int(bool(changing_tau)))
+        if convective_adjust:
+            check(self._lib.cmb200_stepper_update_convective(*head, float(conv_thresh), float(conv_t_multiplier),
+                                                             C.c_void_p(stream)))
+        else:
+            check(self._lib.cmb200_stepper_update(*head, C.c_void_p(stream)))
         return self.delta_net_flux
 
     @property
@@ -69,3 +83,30 @@ class ColumnStepper:
                                              ind.ctypes.data_as(C.POINTER(C.c_int32)),
                                              rem.ctypes.data_as(C.POINTER(C.c_int32))))
         return {'DeltaT': dT, 'dt': dt, 'MaxTendInd': ind, 'n_removed': rem}
+
+
+def convective_adjustment_device(p, T, conv_thresh=1e-5):
+    """``convective_adjustment(p, T)`` (convective_adjustment.py:118-135) for many columns on the GPU.
+    p [nz] cell-centre pressures in either order; T: torch float64 CUDA tensor [n_col, nz] in the
+    same level order as p, adjusted in place.  Returns (T, status[n_col]); status 1 marks columns in
+    which an unstable run reached the top level (where the reference raises IndexError)."""
+    import torch
+    from .convective_adjustment import g, c_p_dry, p_surface_earth, R_specific
+    p = np.asarray(p, dtype=float).reshape(-1)
+    if T.dim() != 2 or T.shape[1] != p.size or T.dtype != torch.float64 or not T.is_contiguous():
+        raise ValueError('T must be a contiguous float64 tensor [n_col, %d]' % p.size)
+    surface_first = p[0] > p[1]
+    p_ref = np.ascontiguousarray(p if surface_first else p[::-1])
+    pw = np.ascontiguousarray((p_ref / p_surface_earth) ** (R_specific * (g / c_p_dry) / g))
+    dev = T.device
+    work = T.flip(1).contiguous() if surface_first else T          # the kernel's level order: top first
+    status = torch.zeros(T.shape[0], dtype=torch.int32, device=dev)
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    p_dev, pw_dev = torch.tensor(p_ref, device=dev), torch.tensor(pw, device=dev)      # alive until the sync below
+    check(_lib.load().cmb200_convective_adjust(p.size, T.shape[0], p_dev.data_ptr(), pw_dev.data_ptr(),
+                                               float(conv_thresh), work.data_ptr(), None, None, status.data_ptr(),
+                                               C.c_void_p(stream)))
+    torch.cuda.current_stream(dev).synchronize()
+    if surface_first:
+        T.copy_(work.flip(1))
+    return T, status

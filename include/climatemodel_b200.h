@@ -197,6 +197,28 @@ int cmb200_stepper_destroy(cmb200_stepper *stepper);
 int cmb200_stepper_update(cmb200_stepper *stepper, const double *net, double *T, double *t,
                           double *delta_net_flux, double net_flux_thresh,
                           double net_flux_percentile, int changing_tau, void *stream);
+/* ---- f2  dry convective adjustment, batched over columns on the device ----------------------- */
+/* convective_adjustment_single (convective_adjustment.py:7-135) for every column.  DEVICE
+ * pointers: p_centre[n_levels] cell-centre pressures, SURFACE FIRST (descending, the reference's
+ * order), p_power[n_levels] = (p_centre / p_reference)^(R lapse / g) evaluated by the caller;
+ * T[n_col][n_levels] in this library's order (top of atmosphere first), adjusted in place.
+ * Optional: active[n_col][n_levels] (levels to report on, surface first; NULL = all),
+ * convective_levels[n_col][n_levels] out = active levels moved by more than conv_thresh
+ * (base.py:189-192), status[n_col] out (0 ok, 1 an unstable run reached the top level -- where
+ * the reference raises IndexError -- and was left alone, 2 iteration cap). */
+int cmb200_convective_adjust(int32_t n_levels, int64_t n_col, const double *p_centre,
+                             const double *p_power, double conv_thresh, double *T,
+                             const uint8_t *active, uint8_t *convective_levels, int32_t *status,
+                             void *stream);
+/* Host arrays p_centre / p_power as above, copied to the stepper; then
+ * cmb200_stepper_update_convective = update_temp with convective_adjust=True (base.py:166-196):
+ * the step, times conv_t_multiplier when the level that sets it was convecting, then the
+ * adjustment. */
+int cmb200_stepper_set_convection(cmb200_stepper *stepper, const double *p_centre, const double *p_power);
+int cmb200_stepper_update_convective(cmb200_stepper *stepper, const double *net, double *T, double *t,
+                                     double *delta_net_flux, double net_flux_thresh,
+                                     double net_flux_percentile, int changing_tau, double conv_thresh,
+                                     double conv_t_multiplier, void *stream);
 /* Copies of the per-column state to HOST arrays of n_col entries (any may be NULL);
  * max_tend_ind counts levels from the surface like the reference. */
 int cmb200_stepper_state(const cmb200_stepper *stepper, double *delta_T, double *dt,

@@ -89,3 +89,77 @@ def test_changing_tau_and_reset():
     assert np.all(t3 > 0) and np.all(t3 == t3[0])                     # identical columns stay identical
     cols.reset()
     assert np.all(cols.t.cpu().numpy() == 0) and np.all(cols.state()['MaxTendInd'] == -1)
+
+
+# ---- dry convective adjustment on the device -------------------------------------
+def test_convective_adjustment_equals_reference_vectors():
+    """The 24 profiles of tests/golden/host_convective.npz (unmodified reference, both pressure
+    orders): the device kernel must return the same bits."""
+    import os
+    import torch
+    from util import GOLDEN
+    from climatemodel_b200.radiation.columns import convective_adjustment_device
+    c = np.load(os.path.join(GOLDEN, 'host_convective.npz'))
+    dev = torch.device('cuda', 0)
+    changed = 0
+    for order in (True, False):                       # group the profiles by pressure order, batch each group
+        idx = [i for i in range(c['p'].shape[0]) if (c['p'][i][0] > c['p'][i][1]) == order]
+        T = torch.tensor(np.ascontiguousarray(c['T'][idx]), device=dev)
+        out, status = convective_adjustment_device(c['p'][idx[0]], T)
+        assert np.all(status.cpu().numpy() == 0)
+        assert np.array_equal(out.cpu().numpy(), c['T_adjusted'][idx])
+        changed += int((np.abs(c['T_adjusted'][idx] - c['T'][idx]).max(axis=1) > 1e-3).sum())
+    assert changed >= 6
+
+
+def test_convective_adjustment_random_profiles_equal_host():
+    import torch
+    from climatemodel_b200.radiation.columns import convective_adjustment_device
+    from climatemodel_b200.radiation.convective_adjustment import convective_adjustment
+    rng = np.random.default_rng(12)
+    for nz in (9, 40, 99, 150):
+        p = np.logspace(np.log10(101320.0), np.log10(30.0), nz)
+        T = 215 + 75 * (p / p[0]) ** rng.uniform(0.1, 0.7, (64, 1)) + rng.normal(0, rng.uniform(0, 5, (64, 1)), (64, nz))
+        lid = max(3, nz // 8)
+        T[:, -lid:] = T[:, -lid - 1:-lid] + np.linspace(5.0, 60.0, lid)   # a stable lid (the reference indexes above unstable runs)
+        want = convective_adjustment(p, T.T.copy()).T
+        got, status = convective_adjustment_device(p, torch.tensor(T, device=torch.device('cuda', 0)))
+        assert np.all(status.cpu().numpy() == 0)
+        assert np.array_equal(got.cpu().numpy(), want), nz
+        if nz >= 40:
+            assert (np.abs(want - T).max(axis=1) > 1e-3).sum() >= 5
+
+
+def test_device_steps_with_convection_equal_host_steps():
+    import torch
+    from climatemodel_b200.plan import FluxPlan
+    from climatemodel_b200.radiation.columns import ColumnStepper
+    c = load_case('co2_nz50_earth')
+    order = np.argsort(c['P'])
+    P = c['P'][order]
+    L = P.size
+    plan = FluxPlan(P, c['nu'], c['bands'], tables=c['tables'])
+    rng = np.random.default_rng(9)
+    n_col = 5
+    T0 = c['T'][np.argsort(c['p'])] + rng.normal(0, 2, (n_col, L - 1))
+    T0[:, -12:] += np.linspace(0, 14, 12)                      # warm lower troposphere: super-adiabatic
+    T_g = c['T_g'] + rng.normal(0, 3, n_col)
+    dev = torch.device('cuda', 0)
+    cols = ColumnStepper(plan, torch.tensor(T0, device=dev), torch.tensor(T_g, device=dev),
+                         q=torch.tensor(np.ascontiguousarray(c['q'][:, order]), device=dev), albedo=0.3)
+    host = host_columns(P[::-1].copy(), T0)
+    t_host = np.zeros(n_col)
+    moved = 0
+    for step in range(40):
+        T_before = cols.T.cpu().numpy().copy()
+        dnf = cols.step(convective_adjust=True, conv_thresh=1e-9, conv_t_multiplier=3).cpu().numpy()
+        net = cols.net_flux.cpu().numpy()
+        T_dev, t_dev, st = cols.T.cpu().numpy(), cols.t.cpu().numpy(), cols.state()
+        for i, atm in enumerate(host):
+            t_host[i], dnf_host = atm.update_temp(t_host[i], net[i][::-1].reshape(-1, 1).copy(), convective_adjust=True,
+                                                   conv_thresh=1e-9, conv_t_multiplier=3)
+            assert np.array_equal(atm.T[::-1, 0], T_dev[i]), (step, i)
+            assert t_host[i] == t_dev[i] and atm.time_step_info['dt'] == st['dt'][i], (step, i)
+            assert dnf_host == dnf[i], (step, i)
+            moved += len(atm.time_step_info['convective_levels']) > 0
+    assert moved >= 5                                           # every column convected at least once
