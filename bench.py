@@ -13,9 +13,12 @@ Planck -> up/down sweeps -> band sums -> net flux and heating rate.
 `value`  : inputs resident in HBM, CUDA events on the launch stream.
 `e2e`    : the same evaluation through the host-buffer C-ABI call (cmb200_flux_host): pinned host
            inputs copied H2D and net flux + heating rate copied D2H inside the timed region.
-N > 1    : the spectrum is sharded across ranks by wavenumber segment (cost-balanced), each rank
-           evaluates its share for all columns and one NCCL all-reduce adds the partial net flux /
-           heating rate (strong scaling).
+N > 1    : N = G column groups x S wavenumber shards.  The S ranks of a group evaluate the same
+           columns, each over its cost-balanced share of the wavenumber segments, and one NCCL
+           all-reduce inside the group adds the partial net flux / heating rate; S is the largest
+           divisor of N that keeps the kernel's per-warp work split balanced
+           (plan.wavenumber_shards; --wavenumber-shards overrides), the G groups split the columns.
+           Total work is fixed as N grows (strong scaling); e2e goes through FluxPlan.flux_sharded.
 """
 import argparse
 import json
@@ -56,6 +59,9 @@ def parse():
     ap.add_argument('--cpu-sample', type=int, default=16, help='columns timed for cpu_baseline')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
+    ap.add_argument('--wavenumber-shards', type=int, default=0,
+                    help='N>1: ranks sharing one set of columns (default: plan.wavenumber_shards rule); '
+                         'the remaining factor of N splits the columns')
     return ap.parse_args()
 
 
@@ -195,10 +201,26 @@ def run_b200(a):
     w = synthetic.workload(a.dnu, a.nz, a.bands)
     plan = FluxPlan(w['P'], w['nu'], w['bands'], tables=w['tables'], precision=a.precision, device=local)
     L, N, M = plan.L, plan.N, plan.M
+    # N ranks = G column groups x S wavenumber shards.  The S ranks of a group evaluate
+    # the same columns, each over its share of the spectrum, and one all-reduce inside the group adds the
+    # partial net flux / heating rate; groups are independent.  S is as large as the spectrum allows
+    # (plan.wavenumber_shards: every warp keeps a run of segments long enough to balance).
+    S, G, group = 1, 1, None
     if world > 1:
-        plan.shard_by_wavenumber(rank, world)
-    n_col = a.columns
-    T, T_g, T_tau, q, albedo = synthetic.columns(n_col, w['P'], seed=0)
+        from climatemodel_b200.plan import wavenumber_shards
+        S = a.wavenumber_shards or wavenumber_shards(plan.segments()[1].size, world)
+        if world % S:
+            raise SystemExit('--wavenumber-shards must divide the number of ranks')
+        G = world // S
+        for g in range(G):                                  # every rank creates every group
+            grp = dist.new_group(list(range(g * S, (g + 1) * S)))
+            if g == rank // S:
+                group = grp
+        plan.shard_by_wavenumber(rank % S, S, **({'lw_cost': float(os.environ['CMB200_SHARD_LW_COST'])}
+                                                 if 'CMB200_SHARD_LW_COST' in os.environ else {}))
+    n_total = a.columns
+    n_col = n_total * (rank // S + 1) // G - n_total * (rank // S) // G
+    T, T_g, T_tau, q, albedo = synthetic.columns(n_col, w['P'], seed=rank // S)
 
     def pinned(x):
         t = torch.empty(x.shape, dtype=torch.float64, pin_memory=True)
@@ -211,8 +233,8 @@ def run_b200(a):
 
     def step():
         plan.flux_device(dT, dTg, T_tau=dTt, q=dq, albedo=dal, outputs=('net', 'heating'), out=out)
-        if world > 1:
-            dist.all_reduce(out_buf)
+        if S > 1:
+            dist.all_reduce(out_buf, group=group)
 
     def barrier():
         if world > 1:
@@ -232,8 +254,8 @@ def run_b200(a):
         kev[i][0].record()
         plan.flux_device(dT, dTg, T_tau=dTt, q=dq, albedo=dal, outputs=('net', 'heating'), out=out)
         kev[i][1].record()
-        if world > 1:
-            dist.all_reduce(out_buf)
+        if S > 1:
+            dist.all_reduce(out_buf, group=group)
         ev[i + 1].record()
     barrier()
     launches = _lib.launch_count() - n0
@@ -243,9 +265,12 @@ def run_b200(a):
     if world > 1:
         t = torch.tensor([total_ms, kernel_ms], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        per_rank = [torch.zeros(2, dtype=torch.float64, device=dev) for _ in range(world)]
+        dist.all_gather(per_rank, torch.tensor([total_ms, kernel_ms], dtype=torch.float64, device=dev))
+        per_rank_kernel_ms = [round(float(x[1]), 3) for x in per_rank]
         total_ms, kernel_ms = t.tolist()
     ms_per_step = total_ms / a.steps
-    units = n_col * L * N
+    units = n_total * L * N
     value = units / (ms_per_step * 1e-3)
 
     # ---- end to end through the host-buffer C ABI -----------------------------------------------------
@@ -254,26 +279,30 @@ def run_b200(a):
         h_out = {'net': torch.empty((n_col, L), dtype=torch.float64, pin_memory=True).numpy(),
                  'heating': torch.empty((n_col, L - 1), dtype=torch.float64, pin_memory=True).numpy()}
         args = dict(T_tau=hTt.numpy(), q=hq.numpy(), albedo=hal.numpy(), outputs=('net', 'heating'), out=h_out)
-        plan.flux(hT.numpy(), hTg.numpy(), **args)
+
+        def e2e_step():
+            if S > 1:                     # copies in, kernel, all-reduce on the device, copies out -- per chunk
+                plan.flux_sharded(hT.numpy(), hTg.numpy(), hTt.numpy(), hq.numpy(), hal.numpy(), h_out, group=group)
+            else:
+                plan.flux(hT.numpy(), hTg.numpy(), **args)
+        e2e_step()
         barrier()
         t0 = time.perf_counter()
         k_e2e = min(a.steps, 3)
         for _ in range(k_e2e):
-            res = plan.flux(hT.numpy(), hTg.numpy(), **args)
-            if world > 1:
-                r = torch.from_numpy(np.concatenate((res['net'].ravel(), res['heating'].ravel()))).to(dev)
-                dist.all_reduce(r)
-                r.cpu()
+            e2e_step()
         barrier()
         dt = (time.perf_counter() - t0) / k_e2e
         if world > 1:
             tt = torch.tensor([dt], dtype=torch.float64, device=dev)
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             dt = tt.item()
-        h2d = sum(x.numel() * 8 for x in (hT, hTg, hTt, hq, hal))
-        d2h = n_col * (2 * L - 1) * 8
+        h2d = sum(x.numel() * 8 for x in (hT, hTg, hTt, hq, hal)) * world          # every rank copies its columns in
+        d2h = n_col * (2 * L - 1) * 8 * world                                       # ... and the reduced result out
         e2e = {'value': units / dt, 'unit': UNIT, 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
-               'ms_per_step': dt * 1e3, 'api': 'cmb200_flux_host via FluxPlan.flux (pinned host buffers)'}
+               'ms_per_step': dt * 1e3,
+               'api': 'FluxPlan.flux_sharded: pinned host buffers, cmb200_flux + NCCL all-reduce per chunk' if S > 1
+               else 'cmb200_flux_host via FluxPlan.flux (pinned host buffers)'}
 
     if rank != 0:
         if world > 1:
@@ -286,13 +315,14 @@ def run_b200(a):
     chains_lw = int(w['bands']['len'][~sw].sum())
     chains_sw = int(w['bands']['len'][sw].sum())
     per_sw = 2 * M + 2 + EXP_FLOPS[a.precision] + 8
-    flops = n_col * (L - 1) * (chains_sw * per_sw + chains_lw * (per_sw + 14)) / world
+    flops = n_col * (L - 1) * (chains_sw * per_sw + chains_lw * (per_sw + 14)) / S      # this rank's launch
     key = 'fp64_tflops' if a.precision == 'f64' else 'fp32_tflops'
     achieved = flops / (kernel_ms * 1e-3) / 1e12
     roofline = {'bound': 'fp64' if a.precision == 'f64' else 'fp32', 'achieved': achieved, 'peak': peaks[key],
                 'unit': 'TFLOP/s', 'frac': achieved / peaks[key], 'traffic': None,
                 'kernel': 'flux_kernel<%s, fused>' % ('double' if a.precision == 'f64' else 'float'),
                 'kernel_ms': kernel_ms,
+                **({'per_rank_kernel_ms': per_rank_kernel_ms} if world > 1 else {}),
                 'peak_source': 'cmb200_measure_peaks: independent-FMA issue-rate microbenchmark on this GPU '
                                '(MEASURED_PEAKS.json has no FP64/FP32 vector peak)',
                 'hbm': {'algorithmic_bytes_per_step': int(n_col * ((L - 1) + 1 + L + M * L + 1 + 2 * L - 1) * 8),
@@ -307,7 +337,7 @@ def run_b200(a):
     # dram__bytes_write.sum = 120.5 MB for 8880 columns of this workload, profiles/r01_flux_kernel_v6_ncu_full.txt),
     # scaled per column to this launch; only meaningful for the default FP64 workload shape.
     if a.precision == 'f64' and (L, M, w['nu'].size) == (100, 2, 10400):
-        roofline['traffic'] = NCU_DRAM_BYTES_PER_COLUMN * n_col / world
+        roofline['traffic'] = NCU_DRAM_BYTES_PER_COLUMN * n_col
         roofline['traffic_source'] = 'ncu dram bytes per column (8880-column capture) x columns of this launch'
 
     cpu = None
@@ -327,8 +357,8 @@ def run_b200(a):
     line = {'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': a.steps, 'warmup': a.warmup,
             'ms_per_step': ms_per_step, 'higher_is_better': True, 'scaling': 'strong', 'vs_baseline': None,
             'dtype': a.precision, 'data': 'synthetic',
-            'config': config_dict(a, w, {'parallelism': 'wavenumber-segment sharding x%d + NCCL all-reduce of net/heating' % world
-                                         if world > 1 else 'single GPU'}),
+            'config': config_dict(a, w, {'parallelism': '%d column group(s) x %d wavenumber shards, NCCL all-reduce of net/heating inside a group'
+                                         % (G, S) if world > 1 else 'single GPU'}),
             'clocks': clocks, 'e2e': e2e, 'gpu_launches': launches, 'roofline': roofline, 'cpu_baseline': cpu,
             'peaks_measured_here': peaks}
     print(json.dumps(line))

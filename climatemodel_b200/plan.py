@@ -45,13 +45,25 @@ def segment_table(band_len, band_sw, bins_per_segment=32):
     return seg_band, ~np.asarray(band_sw).astype(bool)[seg_band]
 
 
-def shard_edges(is_lw, world_size, lw_cost=2.5):
+def shard_edges(is_lw, world_size, lw_cost=2.55):
     """Cut the segment list into ``world_size`` contiguous ranges of equal estimated cost (a
     long-wave segment also runs the emission recurrences and, being alone in its band, pays a
     replay-only pass).  Returns world_size + 1 edges; rank r owns [edges[r], edges[r + 1])."""
     cost = np.cumsum(np.where(is_lw, lw_cost, 1.0))
     inner = [int(np.searchsorted(cost, cost[-1] * r / world_size)) for r in range(1, world_size)]
     return [0] + inner + [int(np.size(is_lw))]
+
+
+def wavenumber_shards(n_segments, world_size, min_segments=128):
+    """How many ranks should share one set of columns: the largest divisor of ``world_size`` that
+    leaves every shard at least ``min_segments`` segments (16 per warp of the 8-warp CTA -- below
+    that the whole-segment split over the warps no longer balances); the remaining factor of
+    world_size splits the columns, which costs no exchange at all."""
+    best = 1
+    for s in range(1, world_size + 1):
+        if world_size % s == 0 and n_segments >= s * min_segments:
+            best = s
+    return best
 
 
 class FluxPlan:
@@ -126,7 +138,7 @@ class FluxPlan:
     def set_segment_range(self, lo, hi):
         check(self._lib.cmb200_plan_set_segment_range(self._h, int(lo), int(hi)))
 
-    def shard_by_wavenumber(self, rank, world_size, lw_cost=2.5):
+    def shard_by_wavenumber(self, rank, world_size, lw_cost=2.55):
         """Restrict this plan to rank's share of the spectrum: contiguous segment ranges of
         equal estimated cost (a long-wave segment also runs the emission recurrences).  The
         outputs are then partial sums; add them across ranks."""
@@ -282,6 +294,75 @@ class FluxPlan:
         stream = torch.cuda.current_stream(dev).cuda_stream
         check(self._lib.cmb200_flux(self._h, C.byref(io), C.c_void_p(stream)))
         return res
+
+    def flux_sharded(self, T, T_g, T_tau, q, albedo, out, group=None, n_chunks=16):
+        """Host buffers in, host buffers out, on a plan restricted by ``shard_by_wavenumber``
+        (SURVEY.md 8e): every rank streams the SAME columns through its share of the spectrum and
+        the partial net flux / heating rate are added across ranks on the device, chunk by chunk
+        (NCCL all-reduce, the path's one exchange step), before they are copied out -- so after
+        the call ``out['net']`` [n_col, L] and ``out['heating']`` [n_col, L-1] hold the complete
+        result on every rank.  T [n_col, L-1], T_g [n_col], T_tau [n_col, L], q [M, n_col, L] or
+        [M, L], albedo [n_col]: float64 NumPy arrays, page-locked if the copies are to overlap
+        the kernels (three streams: copy in / kernel + all-reduce / copy out)."""
+        import torch
+        import torch.distributed as dist
+        L, M = self.L, self.M
+        dev = torch.device('cuda', self.device)
+        n_col = T.shape[0]
+        per_col_q = q.ndim == 3
+        step = max(1, -(-n_col // n_chunks))
+        step = min(n_col, -(-step // 1184) * 1184)                 # whole waves of 148 CTAs x 8 warps
+        st = getattr(self, '_sharded_state', None)
+        if st is None or st['step'] != step or st['per_col_q'] != per_col_q:
+            def buf(*shape):
+                return [torch.empty(shape, dtype=torch.float64, device=dev) for _ in range(2)]
+            st = {'step': step, 'per_col_q': per_col_q, 'T': buf(step, L - 1), 'T_g': buf(step),
+                  'T_tau': buf(step, L), 'albedo': buf(step),
+                  'q': buf(M, step, L) if per_col_q else None, 'res': buf(step * (2 * L - 1)),
+                  'streams': [torch.cuda.Stream(dev) for _ in range(3)],
+                  'in_free': [None, None], 'res_free': [None, None]}
+            self._sharded_state = st
+        s_in, s_comp, s_out = st['streams']
+        hT, hTg, hTt, hq, hal = (torch.from_numpy(x) for x in (T, T_g, T_tau, q, albedo))
+        h_net, h_heat = torch.from_numpy(out['net']), torch.from_numpy(out['heating'])
+        q_dev = None if per_col_q else hq.to(dev)
+        last_out = None
+        for i, c0 in enumerate(range(0, n_col, step)):
+            c1, n, b = min(n_col, c0 + step), min(n_col, c0 + step) - c0, i & 1
+            with torch.cuda.stream(s_in):
+                if st['in_free'][b] is not None:
+                    s_in.wait_event(st['in_free'][b])                # the kernel that read this buffer is done
+                st['T'][b][:n].copy_(hT[c0:c1], non_blocking=True)
+                st['T_g'][b][:n].copy_(hTg[c0:c1], non_blocking=True)
+                st['T_tau'][b][:n].copy_(hTt[c0:c1], non_blocking=True)
+                st['albedo'][b][:n].copy_(hal[c0:c1], non_blocking=True)
+                if per_col_q:
+                    qb = st['q'][b].view(-1)[:M * n * L].view(M, n, L)
+                    for m in range(M):
+                        qb[m].copy_(hq[m, c0:c1], non_blocking=True)
+                ready = s_in.record_event()
+            with torch.cuda.stream(s_comp):
+                s_comp.wait_event(ready)
+                if st['res_free'][b] is not None:
+                    s_comp.wait_event(st['res_free'][b])              # its previous content has been copied out
+                res = st['res'][b][:n * (2 * L - 1)]
+                views = {'net': res[:n * L].view(n, L), 'heating': res[n * L:].view(n, L - 1)}
+                self.flux_device(st['T'][b][:n], st['T_g'][b][:n], T_tau=st['T_tau'][b][:n],
+                                 q=st['q'][b].view(-1)[:M * n * L].view(M, n, L) if per_col_q else q_dev,
+                                 albedo=st['albedo'][b][:n], outputs=('net', 'heating'), out=views)
+                st['in_free'][b] = s_comp.record_event()
+                if dist.is_initialized() and dist.get_world_size(group) > 1:
+                    dist.all_reduce(res, group=group)
+                done = s_comp.record_event()
+            with torch.cuda.stream(s_out):
+                s_out.wait_event(done)
+                h_net[c0:c1].copy_(views['net'], non_blocking=True)
+                h_heat[c0:c1].copy_(views['heating'], non_blocking=True)
+                st['res_free'][b] = last_out = s_out.record_event()
+        if last_out is not None:
+            last_out.synchronize()
+        st['in_free'], st['res_free'] = [None, None], [None, None]
+        return out
 
     def optical_depth_device(self, q, T_tau=None, T_g=None, n_col=None):
         """tau [n_col, L, N] (torch, float64) from the plan's tables (optical_depth,

@@ -99,3 +99,11 @@ def test_oracle_partial_sums_follow_the_kernel_rule():
                                   segment_range=(a, b)) for a, b in zip(cuts[:-1], cuts[1:])]
     for k in (0, 1):
         assert relmax(sum(p[k] for p in parts), full[k]) < 1e-13
+
+
+def test_wavenumber_shard_count_rule():
+    """Ranks sharing one set of columns: as many as leave >= 128 segments each, and a divisor of N."""
+    from climatemodel_b200.plan import wavenumber_shards
+    assert [wavenumber_shards(332, n) for n in (1, 2, 4, 8)] == [1, 2, 2, 2]        # bench workload, 10.4k bins
+    assert [wavenumber_shards(31250, n) for n in (2, 4, 8)] == [2, 4, 8]            # 1M-bin sweep
+    assert wavenumber_shards(100, 8) == 1 and wavenumber_shards(400, 6) == 3
