@@ -43,11 +43,21 @@ static double cost_knob(const char *name, double dflt) {
 // of segments of equal estimated cost, and one partial-sum slot per (part, band) run.
 static int ensure_partition(cmb200_plan *p, int64_t n_col, int W, int resident_ctas) {
     Partition &pt = p->partition;
+    // CTAs per column: with few columns a column is split over C CTAs so that the n_col * C tasks fill
+    // the resident CTAs in whole waves -- pick the C with the least (waves / C), a little bias to small C.
     int C = 1;
-    if (n_col < resident_ctas) {
-        const int64_t want = (resident_ctas + n_col - 1) / n_col;
+    if (n_col < 4 * (int64_t)resident_ctas) {
         const int64_t most = std::max<int64_t>(1, p->n_seg / (2 * W));   // keep two segments per warp
-        C = (int)std::max<int64_t>(1, std::min(want, most));
+        const int64_t top = std::min<int64_t>(most, std::max<int64_t>(4, 2 * ((resident_ctas + n_col - 1) / n_col)));
+        double best = 0.0;
+        for (int64_t c = 1; c <= top; ++c) {
+            const int64_t waves = (n_col * c + resident_ctas - 1) / resident_ctas;
+            const double t = (double)waves / c * (1.0 + 0.005 * c);
+            if (c == 1 || t < best) {
+                best = t;
+                C = (int)c;
+            }
+        }
     }
     if (pt.n_col >= 0 && pt.warps == W && pt.ctas_per_col == C) return CMB200_OK;   // same decomposition
     const int parts = C * W, n_seg = p->n_seg;
@@ -228,9 +238,14 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
         }
     }
     if (C > 1) {
-        flux_finalize_kernel<<<(unsigned)io->n_col, 128, L * sizeof(double), s>>>(
-            L, p->B, p->band_lo, p->band_hi, pt.n_slots, io->n_col, pt.band_slot0.p, p->band_delta.p,
-            p->scratch.p, p->P.p, a.g_over_cp, io->up, io->down, io->net, io->heating);
+        if (p->band_hi > p->band_lo) {
+            flux_band_sums_kernel<<<dim3((unsigned)io->n_col, (unsigned)(p->band_hi - p->band_lo)), std::min(512, (2 * L + 31) / 32 * 32), 0, s>>>(
+                L, p->B, p->band_lo, pt.n_slots, pt.band_slot0.p, p->scratch.p, io->up, io->down);
+            CMB_LAUNCHED();
+        }
+        flux_net_kernel<<<(unsigned)io->n_col, 128, L * sizeof(double), s>>>(
+            L, p->band_lo, p->band_hi, pt.n_slots, pt.band_slot0.p, p->band_delta.p, p->scratch.p, p->P.p,
+            a.g_over_cp, io->net, io->heating);
         CMB_LAUNCHED();
     }
     return CMB200_OK;
@@ -367,7 +382,8 @@ extern "C" int cmb200_flux(cmb200_plan *plan, const cmb200_flux_io *io, void *st
     }
     {
         const int warps = 4;
-        interface_temperature_kernel<<<(unsigned)((io->n_col + warps - 1) / warps), warps * 32, 0, s>>>(
+        const int64_t items = io->n_col * ((L + 31) / 32);
+        interface_temperature_kernel<<<(unsigned)((items + warps - 1) / warps), warps * 32, 0, s>>>(
             L, io->n_col, plan->splineT.p, io->T, io->T_g, Tint);
         CMB_LAUNCHED();
     }

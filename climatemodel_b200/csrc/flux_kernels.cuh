@@ -765,7 +765,7 @@ __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
             a.dbg[warp] = clock64() - t_sweep0;
             a.dbg[32 + warp] = t_sweep0 - t_task0;
         }
-        if (C != 1) continue;      // several CTAs per column: flux_finalize_kernel adds the slots up
+        if (C != 1) continue;      // several CTAs per column: flux_band_sums_kernel + flux_net_kernel finish
 
         // ---- column epilogue: band sums, net flux (:712-713), heating rate (base.py:166-168) ----------
         __syncthreads();
@@ -813,29 +813,50 @@ __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
     }
 }
 
-// Split mode (few columns): sums the per-(part, band) partial sweeps in slot order, then the
-// same band -> net -> heating epilogue.  One warp per column, lanes over interfaces.
-__global__ void flux_finalize_kernel(int L, int B, int band_lo, int band_hi, int n_slots,
-                                     int64_t n_col, const int32_t *__restrict__ band_slot0,
-                                     const double *__restrict__ band_delta,
-                                     const double *__restrict__ scratch,
-                                     const double *__restrict__ Pint, double g_over_cp,
-                                     double *up, double *down, double *net, double *heating) {
+// Split mode (few columns), two small kernels.  flux_band_sums_kernel: one CTA per (column, band),
+// one thread per (direction, interface); adds the band's per-part partial sweeps in slot order
+// (loads issued eight at a time, the adds stay sequential) and leaves the band sum in the band's
+// first slot.  flux_net_kernel: one CTA per column, band sums -> net flux (:712-713) -> heating
+// rate (base.py:166-168), as in the fused epilogue.
+__global__ void flux_band_sums_kernel(int L, int B, int band_lo, int n_slots,
+                                      const int32_t *__restrict__ band_slot0, double *scratch,
+                                      double *up, double *down) {
+    const int64_t col = blockIdx.x;
+    const int j = band_lo + blockIdx.y;
+    const int q0 = band_slot0[j], q1 = band_slot0[j + 1];
+    for (int idx = threadIdx.x; idx < 2 * L; idx += blockDim.x) {
+        const int half = idx >= L, i = idx - half * L;
+        double *v = scratch + col * n_slots * 2 * (int64_t)L + idx;
+        double sum = 0.0;
+        int q = q0;
+        for (; q + 8 <= q1; q += 8) {
+            double x[8];
+#pragma unroll
+            for (int r = 0; r < 8; ++r) x[r] = v[(q + r) * 2 * (int64_t)L];
+#pragma unroll
+            for (int r = 0; r < 8; ++r) sum += x[r];
+        }
+        for (; q < q1; ++q) sum += v[q * 2 * (int64_t)L];
+        if (q0 < q1) v[q0 * 2 * (int64_t)L] = sum;
+        double *out = half ? down : up;
+        if (out) out[(col * L + i) * B + j] = sum;
+    }
+}
+
+__global__ void flux_net_kernel(int L, int band_lo, int band_hi, int n_slots,
+                                const int32_t *__restrict__ band_slot0,
+                                const double *__restrict__ band_delta, const double *__restrict__ scratch,
+                                const double *__restrict__ Pint, double g_over_cp, double *net, double *heating) {
     extern __shared__ double snet[];
     const int64_t col = blockIdx.x;
+    const double *sc = scratch + col * n_slots * 2 * (int64_t)L;
     for (int i = threadIdx.x; i < L; i += blockDim.x) {
         double nu = 0.0, nd = 0.0;
         for (int j = band_lo; j < band_hi; ++j) {
-            double u = 0.0, d = 0.0;
-            for (int s = band_slot0[j]; s < band_slot0[j + 1]; ++s) {
-                const double *o = scratch + ((col * n_slots + s) * 2) * (int64_t)L;
-                u += o[i];
-                d += o[L + i];
-            }
-            if (up) up[(col * L + i) * B + j] = u;
-            if (down) down[(col * L + i) * B + j] = d;
-            nu += u * band_delta[j];
-            nd += d * band_delta[j];
+            const int q0 = band_slot0[j];
+            if (q0 == band_slot0[j + 1]) continue;          // band outside this plan's segment range
+            nu += sc[(q0 * 2) * (int64_t)L + i] * band_delta[j];
+            nd += sc[(q0 * 2 + 1) * (int64_t)L + i] * band_delta[j];
         }
         snet[i] = nu - nd;
         if (net) net[col * L + i] = nu - nd;
@@ -846,24 +867,26 @@ __global__ void flux_finalize_kernel(int L, int B, int band_lo, int band_hi, int
             heating[col * (L - 1) + k] = g_over_cp * (snet[k + 1] - snet[k]) / (Pint[k + 1] - Pint[k]);
 }
 
-// Interface temperatures (real_gas.py:634-636): T_int = A T with A the not-a-knot cubic-spline
-// operator of the (shared) pressure grid, stored transposed At[k][i]; surface value := T_g.
+// T_interface = A T (the not-a-knot spline of real_gas.py:634 as a matrix, At = A transposed:
+// [L-1][L]), T_interface[L-1] = T_g (:636).  One warp per (column, 32 interfaces); the sum runs
+// over the layers in order, loads batched by the unrolling.
 __global__ void interface_temperature_kernel(int L, int64_t n_col, const double *__restrict__ At,
                                              const double *__restrict__ T,
                                              const double *__restrict__ T_g,
                                              double *__restrict__ Tint) {
     const int warps = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int64_t col = (int64_t)blockIdx.x * warps + warp;
+    const int chunks = (L + 31) >> 5;
+    const int64_t item = (int64_t)blockIdx.x * warps + warp;
+    const int64_t col = item / chunks;
     if (col >= n_col) return;
+    const int i = (int)(item - col * chunks) * 32 + lane;
+    if (i >= L) return;
     const int nl = L - 1;
     const double *Tc = T + col * nl;
-    for (int i0 = 0; i0 < L; i0 += 32) {
-        int i = i0 + lane;
-        double acc = 0.0;
-        if (i < L)
-            for (int k = 0; k < nl; ++k) acc += At[k * L + i] * Tc[k];
-        if (i < L) Tint[col * L + i] = (i == L - 1) ? T_g[col] : acc;
-    }
+    double acc = 0.0;
+#pragma unroll 8
+    for (int k = 0; k < nl; ++k) acc += At[k * L + i] * Tc[k];
+    Tint[col * L + i] = (i == L - 1) ? T_g[col] : acc;
 }
 
 }  // namespace cmb
