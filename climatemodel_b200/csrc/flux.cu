@@ -105,10 +105,40 @@ static int ensure_partition(cmb200_plan *p, int64_t n_col, int W, int resident_c
     return CMB200_OK;
 }
 
-template <typename Real, int MM>
+// Warps per CTA of kernel variant V for L interfaces: bounded by shared memory (t-store, accumulators,
+// coefficient rows) and, for the tensor-memory t-store, by the 512 columns of a lane quarter shared
+// by the warps w, w + 4, ...  0 = the variant cannot run this L.
+template <typename Real, int MM, int V>
+static int variant_warps(int L, int max_smem, int *tmem_cpw, int *tmem_cols) {
+    const CtaSmem<Real, MM, V> lay(L);
+    int W = (size_t)max_smem > lay.shared_total
+                ? (int)std::min<size_t>(8, ((size_t)max_smem - lay.shared_total) / lay.warp_total)
+                : 0;
+    *tmem_cpw = *tmem_cols = 0;
+    if (V & kVarTmem) {
+        const int cpw = padded_layers(L) * (int)(sizeof(Real) / 4);
+        const int per_quarter = std::min(2, 512 / cpw);
+        W = std::min(W, 4 * per_quarter) / 4 * 4;      // whole lane quarters
+        int cols = 32;
+        while (cols < per_quarter * cpw) cols *= 2;
+        *tmem_cpw = cpw;
+        *tmem_cols = cols;
+    }
+    return W;
+}
+
+// Default kernel variant (see flux_kernels.cuh); CMB200_FLUX_VARIANT overrides it for experiments.
+constexpr int kDefaultVariant = 0;
+static int flux_variant() {
+    const char *e = getenv("CMB200_FLUX_VARIANT");
+    const int v = e && *e ? atoi(e) : kDefaultVariant;
+    return (v == 1 || v == 3 || v == 7) ? v : 0;
+}
+
+template <typename Real, int MM, int V>
 static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *Tint, cudaStream_t s) {
     const int L = p->L, Lp = padded_layers(L);
-    const CtaSmem<Real, MM> lay(L);
+    const CtaSmem<Real, MM, V> lay(L);
     const double span = MM > 0 ? (double)MM * L * p->nT_pad * (double)p->pitch * sizeof(Real) / 16.0 : (double)L * (double)p->N;
     if (span >= 4294967296.0) {
         set_error("table / tau rows exceed the 32-bit row offsets of the flux kernel (%.3g units)", span);
@@ -116,17 +146,22 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     }
     int max_smem = 0;
     CMB_CUDA(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, p->device));
-    const int W = (size_t)max_smem > lay.shared_total
-                      ? (int)std::min<size_t>(8, ((size_t)max_smem - lay.shared_total) / lay.warp_total)
-                      : 0;
+    int tmem_cpw = 0, tmem_cols = 0;
+    const int W = variant_warps<Real, MM, V>(L, max_smem, &tmem_cpw, &tmem_cols);
+    if constexpr (V != 0) {      // the variant has to offer at least the warps of the plain kernel, else that one runs
+        int c0, c1;
+        if (W < variant_warps<Real, MM, 0>(L, max_smem, &c0, &c1)) return launch_flux<Real, MM, 0>(p, io, Tint, s);
+    }
     if (W < 1) {
         set_error("%d levels need %zu bytes of shared memory per CTA; the device offers %d", L, lay.total(1), max_smem);
         return CMB200_ERR_LIMIT;
     }
-    const size_t smem = lay.total(W);
-    CMB_CUDA(cudaFuncSetAttribute(flux_kernel<Real, MM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    // A CTA that allocates tensor memory must be alone on its SM (a second one would wait for the
+    // columns): ask for more than half of the shared memory.
+    const size_t smem = (V & kVarTmem) ? std::max(lay.total(W), (size_t)max_smem / 2 + 1024) : lay.total(W);
+    CMB_CUDA(cudaFuncSetAttribute(flux_kernel<Real, MM, V>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int ctas_per_sm = 1;
-    CMB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, flux_kernel<Real, MM>, W * 32, smem));
+    CMB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, flux_kernel<Real, MM, V>, W * 32, smem));
     const int resident = sm_count(p->device) * std::max(1, ctas_per_sm);
     int rc = ensure_partition(p, io->n_col, W, resident);
     if (rc) return rc;
@@ -218,7 +253,9 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
         CMB_CUDA(dbg.alloc(64));
         a.dbg = dbg.p;
     }
-    flux_kernel<Real, MM><<<(unsigned)grid, W * 32, smem, s>>>(a);
+    a.tmem_cpw = tmem_cpw;
+    a.tmem_cols = tmem_cols;
+    flux_kernel<Real, MM, V><<<(unsigned)grid, W * 32, smem, s>>>(a);
     CMB_LAUNCHED();
     if (debug_timing) {   // per-warp sweep cycles of CTA 0's first column next to what the partition gave each warp
         long long h[64];
@@ -393,23 +430,33 @@ extern "C" int cmb200_flux(cmb200_plan *plan, const cmb200_flux_io *io, void *st
         if (rc) return rc;
     }
     const int mm = fused ? plan->M : 0;
+    const int variant = flux_variant();
+#define CMB_FLUX_CASE(REAL, M_)                                                     \
+    case M_:                                                                        \
+        switch (variant) {                                                          \
+            case 1: return launch_flux<REAL, M_, 1>(plan, io, Tint, s);             \
+            case 3: return launch_flux<REAL, M_, 3>(plan, io, Tint, s);             \
+            case 7: return launch_flux<REAL, M_, 7>(plan, io, Tint, s);             \
+            default: return launch_flux<REAL, M_, 0>(plan, io, Tint, s);            \
+        }
     if (plan->precision == CMB200_F64) {
         switch (mm) {
-            case 0: return launch_flux<double, 0>(plan, io, Tint, s);
-            case 1: return launch_flux<double, 1>(plan, io, Tint, s);
-            case 2: return launch_flux<double, 2>(plan, io, Tint, s);
-            case 3: return launch_flux<double, 3>(plan, io, Tint, s);
-            case 4: return launch_flux<double, 4>(plan, io, Tint, s);
+            CMB_FLUX_CASE(double, 0)
+            CMB_FLUX_CASE(double, 1)
+            CMB_FLUX_CASE(double, 2)
+            CMB_FLUX_CASE(double, 3)
+            CMB_FLUX_CASE(double, 4)
         }
     } else {
         switch (mm) {
-            case 0: return launch_flux<float, 0>(plan, io, Tint, s);
-            case 1: return launch_flux<float, 1>(plan, io, Tint, s);
-            case 2: return launch_flux<float, 2>(plan, io, Tint, s);
-            case 3: return launch_flux<float, 3>(plan, io, Tint, s);
-            case 4: return launch_flux<float, 4>(plan, io, Tint, s);
+            CMB_FLUX_CASE(float, 0)
+            CMB_FLUX_CASE(float, 1)
+            CMB_FLUX_CASE(float, 2)
+            CMB_FLUX_CASE(float, 3)
+            CMB_FLUX_CASE(float, 4)
         }
     }
+#undef CMB_FLUX_CASE
     set_error("unsupported molecule count %d", mm);
     return CMB200_ERR_LIMIT;
 }

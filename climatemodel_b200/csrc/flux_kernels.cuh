@@ -26,6 +26,7 @@
 // scratch (L2 resident) and are added in a fixed order, so results do not depend on scheduling.
 #pragma once
 #include "internal.cuh"
+#include "tmem.cuh"
 
 namespace cmb {
 
@@ -61,7 +62,20 @@ struct FluxArgs {
     Real *coefbuf;             // [CTA][B][4][Lp] emission coefficients of the long-wave bands
     unsigned long long *task_counter;   // zeroed before the launch
     long long *dbg;            // optional: sweep cycles per warp of CTA 0's first task (CMB200_DEBUG_TIMING)
+    int tmem_cols, tmem_cpw;   // TMEM t-store: columns allocated per CTA, columns per warp (V & kVarTmem)
 };
+
+// Kernel variants (template parameter V, a bit set):
+//   kVarTmem      the t-store lives in tensor memory (one LDTM / STTM per block of kU layers and
+//                 lane) instead of shared memory, which frees 26 kB of shared memory per warp;
+//   kVarCoefSmem  the long-wave emission coefficients of the band a warp is working on are staged in
+//                 its shared memory and read with broadcast 128-bit loads instead of being loaded per
+//                 lane from global memory and broadcast with shuffles;
+//   kVarPartial   the warp reduction of a block stops after two exchange steps and the four-lane
+//                 partial sums are accumulated in shared memory per (interface, lane & 7); the eight
+//                 partials are added when the (warp, band) run is written out.
+constexpr int kVarTmem = 1, kVarCoefSmem = 2, kVarPartial = 4;
+constexpr int kPartialLanes = 8;
 
 constexpr int kU = 8;          // layers per block of a pass (instruction-level parallelism)
 
@@ -118,9 +132,9 @@ __host__ __device__ inline int padded_layers(int L) { return ((L - 1) + kU - 1) 
 
 // Shared-memory layout of one CTA (every sub-array 16-byte aligned): the column's level tables
 // once, then per warp the band accumulators and the t-store.
-template <typename Real, int MM>
+template <typename Real, int MM, int V = 0>
 struct CtaSmem {
-    size_t off_offdn, off_offup, off_qg, off_hdp, shared_total, warp_bacc, warp_ts, warp_total;
+    size_t off_offdn, off_offup, off_qg, off_hdp, shared_total, warp_bacc, warp_coef, warp_ts, warp_total;
     int lev_stride;
     __host__ __device__ CtaSmem(int L) {
         auto up16 = [](size_t x) { return (x + 15) & ~(size_t)15; };
@@ -136,11 +150,23 @@ struct CtaSmem {
         off_hdp = b;
         b = up16(b + (size_t)Lp * sizeof(Real));
         shared_total = b;
-        warp_bacc = 0;                                                     // bacc_up, bacc_dn [Lp + kU] each
-        warp_ts = up16((size_t)2 * (Lp + kU) * sizeof(double));
-        warp_total = up16(warp_ts + (size_t)Lp * 32 * sizeof(Real));
+        // per warp: band accumulators (bacc_up, bacc_dn [Lp + kU] each, or the partial-sum layout
+        // [2][Lp / 2][kPartialLanes][2]), the staged coefficient rows [4][Lp], the t-store [Lp][32]
+        warp_bacc = 0;
+        warp_coef = up16((V & kVarPartial) ? (size_t)2 * Lp * kPartialLanes * sizeof(double)
+                                           : (size_t)2 * (Lp + kU) * sizeof(double));
+        warp_ts = up16(warp_coef + ((V & kVarCoefSmem) ? (size_t)4 * Lp * sizeof(Real) : 0));
+        warp_total = up16(warp_ts + ((V & kVarTmem) ? 0 : (size_t)Lp * 32 * sizeof(Real)));
     }
     __host__ __device__ size_t total(int warps) const { return shared_total + warp_total * warps; }
+};
+
+// Where a warp keeps its t-store: a shared-memory row pointer (already offset by the lane) or a
+// tensor-memory address (lane quarter and first column of the warp).
+template <typename Real>
+struct TStore {
+    Real *lane;
+    uint32_t taddr;
 };
 
 // exp(-x) for the layer transmissivity.  FP64: n = rint(-x log2 e), r = -x - n ln2 (two-term
@@ -278,14 +304,26 @@ __device__ __forceinline__ void prefetch_pass(const bool up, const int Lp, const
 // independent exp evaluations of block b are in flight (stage A), the serial recurrences of block
 // b-1 (stage B, both chains) and the warp reduction of their summed values (stage C) are issued
 // in between, statement by statement -- ptxas keeps this order.
-template <typename Real, int MM, bool LW, bool UP, bool FRESH>
+// Two consecutive, 8/16-byte aligned shared-memory values with one load.
+__device__ __forceinline__ void lds_pair(const double *p, double (&o)[2]) {
+    const double2 v = *reinterpret_cast<const double2 *>(p);
+    o[0] = v.x, o[1] = v.y;
+}
+__device__ __forceinline__ void lds_pair(const float *p, float (&o)[2]) {
+    const float2 v = *reinterpret_cast<const float2 *>(p);
+    o[0] = v.x, o[1] = v.y;
+}
+
+template <typename Real, int MM, bool LW, bool UP, bool FRESH, int V>
 __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const int Lp, const Real wF, const Real wR,
                                            const Real b0, const void *src_lane, const void *next_src,
-                                           PassFeed<Real, MM> &fd, const LevelView<Real> lv, Real *tsl, double *bacc,
-                                           const Real *coefL, const Real *coefG) {
+                                           PassFeed<Real, MM> &fd, const LevelView<Real> lv, const TStore<Real> tst,
+                                           double *bacc, const Real *coefL, const Real *coefG) {
     constexpr bool FUSED = MM > 0;
     constexpr int MR = MM > 0 ? MM : 1;
     constexpr bool F64 = sizeof(Real) == 8;
+    constexpr bool TM = (V & kVarTmem) != 0, CS = (V & kVarCoefSmem) != 0, PA = (V & kVarPartial) != 0;
+    constexpr int WPR = sizeof(Real) / 4, NW = kU * WPR;   // 32-bit words per value / per block and lane
     using Src = typename std::conditional<FUSED, Real, double>::type;
     const char *src_bytes = (const char *)src_lane;
     constexpr unsigned kOffUnit = FUSED ? 16u : 8u;   // table rows are 64-byte aligned, tau rows only 8
@@ -294,6 +332,7 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
     const int ridx = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
     const bool rlane = (lane & 3) == 0;
     const int kfirst = UP ? Lp - kU : 0, kstep = UP ? -kU : kU;
+    Real *const tsl = tst.lane;
 
     // ---- warp reduction of v[0..7], split into five steps for the interleave ----------------------
     Real v[kU], a4[4], a2[2], c1;
@@ -312,33 +351,71 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
         }
     };
     auto C3 = [&]() {
-        const Real keep = h2 ? a2[1] : a2[0], send = h2 ? a2[0] : a2[1];
-        c1 = keep + __shfl_xor_sync(full, send, 4);
+        if constexpr (!PA) {
+            const Real keep = h2 ? a2[1] : a2[0], send = h2 ? a2[0] : a2[1];
+            c1 = keep + __shfl_xor_sync(full, send, 4);
+        }
     };
-    auto C4 = [&]() { c1 += __shfl_xor_sync(full, c1, 2); };
-    auto C5 = [&]() { c1 += __shfl_xor_sync(full, c1, 1); };
-    // band accumulator of the reduced block: fetched early so that the read latency is off the tail
+    auto C4 = [&]() {
+        if constexpr (!PA) c1 += __shfl_xor_sync(full, c1, 2);
+    };
+    auto C5 = [&]() {
+        if constexpr (!PA) c1 += __shfl_xor_sync(full, c1, 1);
+    };
+    // band accumulator of the reduced block: fetched early so that the read latency is off the tail.
+    // Partial mode: after C2 this lane holds the sums over lanes {l, l^8, l^16, l^24} of the two
+    // layers 4 h4 + 2 h3 + {0, 1} of the block -> one 16-byte slot per (layer pair, lane & 7).
     double bold = 0.0;
+    double2 bold2 = make_double2(0.0, 0.0);
+    double2 *const pacc = reinterpret_cast<double2 *>(bacc) + (((lane >> 4) & 1) * 2 + ((lane >> 3) & 1)) * kPartialLanes + (lane & 7);
     auto Cload = [&](int kc) {
-        if (rlane && kc + ridx < nl) bold = bacc[kc + ridx];
+        if constexpr (PA) {
+            bold2 = pacc[(kc >> 1) * kPartialLanes];
+        } else {
+            if (rlane && kc + ridx < nl) bold = bacc[kc + ridx];
+        }
     };
     auto Cstore = [&](int kc) {
-        if (rlane && kc + ridx < nl) bacc[kc + ridx] = bold + (double)c1;
+        if constexpr (PA) {
+            bold2.x += (double)a2[0];
+            bold2.y += (double)a2[1];
+            pacc[(kc >> 1) * kPartialLanes] = bold2;
+        } else {
+            if (rlane && kc + ridx < nl) bacc[kc + ridx] = bold + (double)c1;
+        }
     };
 
     // ---- recurrence step of layer kb+u for both chains (stage B) --------------------------------------
     Real EF = wF * b0, HF = Real(0), ER = wR * b0, HR = Real(0);
     Real tp[kU], tR[kU];
-    // Long-wave emission coefficients live in global memory (L2): one coalesced load per block, a
-    // block ahead, gives lane 8 r + i the coefficient of row r (coefL, coefG = coefL + Lp) and layer
-    // k0 + i; the recurrence broadcasts them with shuffles.
+    // Long-wave emission coefficients.  Default: they live in global memory (L2): one coalesced load
+    // per block, a block ahead, gives lane 8 r + i the coefficient of row r (coefL, coefG = coefL + Lp)
+    // and layer k0 + i; the recurrence broadcasts them with shuffles.  kVarCoefSmem: coefL / coefG
+    // point into the warp's shared memory and two layers (one pair) are read per broadcast load, two
+    // pairs ahead, into the rolling buffers cA / cB ([row][layer parity]).
     const Real *crow = coefL + ((lane >> 3) & 1) * (coefG - coefL) + (lane & (kU - 1));
     Real ccur = Real(0), cnext = Real(0);
-    auto Bstep = [&](int kb, int u, Real(&out)[kU]) {
+    Real cA[2][2] = {{Real(0), Real(0)}, {Real(0), Real(0)}}, cB[2][2] = {{Real(0), Real(0)}, {Real(0), Real(0)}};
+    auto ldpair = [&](int kb, int pi, Real(&c)[2][2]) {
+        if constexpr (LW && CS) {
+            const int k = kb + 2 * (UP ? 3 - pi : pi);
+            lds_pair(coefL + k, c[0]);
+            lds_pair(coefG + k, c[1]);
+        }
+    };
+    auto ord = [](int o) { return UP ? kU - 1 - o : o; };   // order in which a block's layers are swept
+    auto Bstep = [&](int kb, int o, Real(&out)[kU]) {
+        const int u = ord(o);
         Real cl = Real(0), cg = Real(0), valF = Real(0), valR;
         if (LW) {
-            cl = __shfl_sync(full, ccur, u);        // lanes 0-7 hold the block's "last/first" row, 8-15 its "gen" row
-            cg = __shfl_sync(full, ccur, kU + u);
+            if constexpr (CS) {
+                const Real(&c)[2][2] = ((o >> 1) & 1) ? cB : cA;
+                cl = c[0][u & 1];
+                cg = c[1][u & 1];
+            } else {
+                cl = __shfl_sync(full, ccur, u);        // lanes 0-7 hold the block's "last/first" row, 8-15 its "gen" row
+                cg = __shfl_sync(full, ccur, kU + u);
+            }
         }
         if constexpr (FRESH) {
             EF *= tp[u];
@@ -362,7 +439,18 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
         }
         out[u] = FRESH ? valF + valR : valR;
     };
-    auto ord = [](int o) { return UP ? kU - 1 - o : o; };   // order in which a block's layers are swept
+    // Steps 2 pi, 2 pi + 1 of block kb; afterwards the pair buffer they used is refilled with pair
+    // pi + 2 of this block or pair pi - 2 of the next block (knext; < 0: there is none).
+    auto Bpair = [&](int kb, int pi, Real(&out)[kU], int knext) {
+        Bstep(kb, 2 * pi, out);
+        Bstep(kb, 2 * pi + 1, out);
+        if constexpr (LW && CS) {
+            if (pi < 2)
+                ldpair(kb, pi + 2, pi & 1 ? cB : cA);
+            else if (knext >= 0)
+                ldpair(knext, pi - 2, pi & 1 ? cB : cA);
+        }
+    };
 
     if constexpr (FRESH) {
         // raw[u][m]: table value (or tau) of the block's loaded interfaces, fetched one block ahead so
@@ -389,21 +477,33 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
             Ic = fd.icraw[0];
         }
 
-        // t-store traffic of a block, spread over the iteration: once the recurrences are done with
-        // layer kb+u the fresh t (still in tp) is parked in its row, and once they are done with the
-        // whole block the replay chain's t of block k0 is fetched from the rows that block k0's fresh t
-        // will overwrite one iteration later.
-        auto park = [&](int kb, int u) { tsl[(kb + u) * 32] = tp[u]; };
-        auto fetch_replay = [&](int k0) {
+        // t-store traffic of a block.  Shared memory: spread over the iteration -- once the recurrences
+        // are done with layer kb+u the fresh t (still in tp) is parked in its row, and once they are done
+        // with the whole block the replay chain's t of block k0 is fetched from the rows that block k0's
+        // fresh t will overwrite one iteration later.  Tensor memory: the replay block is fetched with one
+        // LDTM at the same point, and at the end of the iteration (after the wait on that load) the fresh
+        // t of block k0 goes to the same columns with one STTM.
+        uint32_t tRw[NW];
 #pragma unroll
-            for (int u = 0; u < kU; ++u) tR[u] = tsl[(k0 + u) * 32];
+        for (int i = 0; i < NW; ++i) tRw[i] = 0u;
+        auto park = [&](int kb, int o) {
+            if constexpr (!TM) tsl[(kb + ord(o)) * 32] = tp[ord(o)];
+        };
+        auto fetch_replay = [&](int k0) {
+            if constexpr (TM) {
+                tmem::ld<NW>(tst.taddr + (uint32_t)(k0 * WPR), tRw);
+            } else {
+#pragma unroll
+                for (int u = 0; u < kU; ++u) tR[u] = tsl[(k0 + u) * 32];
+            }
         };
         auto iter = [&](auto doA_t, auto doB_t, const int k0) {
             constexpr bool DO_A = decltype(doA_t)::value, DO_B = decltype(doB_t)::value;
             const int kb = k0 - kstep;
+            const int knext = DO_A ? k0 : -1;     // the block stage B works on in the next iteration
             Real x[kU], t[kU];
             if (DO_B) Cload(kb);
-            if (LW && DO_A) cnext = crow[k0];
+            if (LW && DO_A && !CS) cnext = crow[k0];
             // stage A set-up: layer integrand at the block's interfaces, next block's loads, dtau
             if (DO_A) {
                 Src In[kU];
@@ -445,7 +545,7 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
                         tn[u] = fma(-x[u], kExpC[11], kExpC[12]);
                     }
                 }
-                if (DO_B) { Bstep(kb, ord(0), v); Bstep(kb, ord(1), v); park(kb, ord(0)); park(kb, ord(1)); }
+                if (DO_B) { Bpair(kb, 0, v, knext); park(kb, 0); park(kb, 1); }
                 if (DO_A) {
 #pragma unroll
                     for (int u = 0; u < kU; ++u) {
@@ -453,12 +553,12 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
                         tn[u] -= kExpC[12];
                     }
                 }
-                if (DO_B) { Bstep(kb, ord(2), v); Bstep(kb, ord(3), v); park(kb, ord(2)); park(kb, ord(3)); }
+                if (DO_B) { Bpair(kb, 1, v, knext); park(kb, 2); park(kb, 3); }
                 if (DO_A) {
 #pragma unroll
                     for (int u = 0; u < kU; ++u) r[u] = fma(tn[u], kExpC[13], -x[u]);
                 }
-                if (DO_B) { Bstep(kb, ord(4), v); Bstep(kb, ord(5), v); park(kb, ord(4)); park(kb, ord(5)); }
+                if (DO_B) { Bpair(kb, 2, v, knext); park(kb, 4); park(kb, 5); }
                 if (DO_A) {
 #pragma unroll
                     for (int u = 0; u < kU; ++u) {
@@ -466,7 +566,7 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
                         p[u] = kExpC[0];
                     }
                 }
-                if (DO_B) { Bstep(kb, ord(6), v); Bstep(kb, ord(7), v); park(kb, ord(6)); park(kb, ord(7)); }
+                if (DO_B) { Bpair(kb, 3, v, knext); park(kb, 6); park(kb, 7); }
                 if (DO_A) fetch_replay(k0);
 #pragma unroll
                 for (int i = 1; i <= 10; ++i) {
@@ -496,9 +596,10 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
                 }
                 if (DO_B) {
 #pragma unroll
-                    for (int o = 0; o < kU; ++o) {
-                        Bstep(kb, ord(o), v);
-                        park(kb, ord(o));
+                    for (int pi = 0; pi < kU / 2; ++pi) {
+                        Bpair(kb, pi, v, knext);
+                        park(kb, 2 * pi);
+                        park(kb, 2 * pi + 1);
                     }
                 }
                 if (DO_A) fetch_replay(k0);
@@ -506,9 +607,20 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
             }
             if (DO_B) Cstore(kb);
             if (DO_A) {
+                if constexpr (TM) {
+                    tmem::wait_ld<NW>(tRw);
+                    tmem::unpack<kU>(tRw, tR);
+                    uint32_t tw[NW];
+                    tmem::pack<kU>(t, tw);
+                    tmem::st<NW>(tst.taddr + (uint32_t)(k0 * WPR), tw);
+                }
 #pragma unroll
                 for (int u = 0; u < kU; ++u) tp[u] = t[u];
                 ccur = cnext;
+                if (!DO_B) {          // first iteration of the pass: both coefficient pair buffers are empty
+                    ldpair(k0, 0, cA);
+                    ldpair(k0, 1, cB);
+                }
             }
         };
         iter(std::true_type{}, std::false_type{}, kfirst);
@@ -521,43 +633,80 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
             if (next_src) prefetch_pass<Real, MM>(!UP, Lp, next_src, lv, fd);   // raw is free from here on
             iter(std::false_type{}, std::true_type{}, Lp);
         }
+        if constexpr (TM) tmem::wait_st();   // the next pass reads these columns back
     } else {
         // ---- replay only: recurrence of block b interleaved with the reduction of the block before --
         Real tn8[kU], vp[kU];
+        uint32_t tnw[NW];
+#pragma unroll
+        for (int i = 0; i < NW; ++i) tnw[i] = 0u;
         auto iter = [&](auto doB_t, auto doC_t, const int k0) {
             constexpr bool DO_B = decltype(doB_t)::value, DO_C = decltype(doC_t)::value;
+            const bool more = DO_B && (UP ? k0 >= kU : k0 + kU < Lp);
+            const int knext = more ? k0 + kstep : -1;
             if (DO_C) Cload(k0 - kstep);
-            if (DO_B && (UP ? k0 >= kU : k0 + kU < Lp)) {
+            if (more) {
+                if constexpr (TM) {
+                    tmem::ld<NW>(tst.taddr + (uint32_t)((k0 + kstep) * WPR), tnw);
+                } else {
 #pragma unroll
-                for (int u = 0; u < kU; ++u) tn8[u] = tsl[(k0 + kstep + u) * 32];
-                if (LW) cnext = crow[k0 + kstep];
+                    for (int u = 0; u < kU; ++u) tn8[u] = tsl[(k0 + kstep + u) * 32];
+                }
+                if (LW && !CS) cnext = crow[k0 + kstep];
             }
-            if (DO_B) Bstep(k0, ord(0), vp);
+            if (DO_B) Bstep(k0, 0, vp);
             if (DO_C) C1();
-            if (DO_B) { Bstep(k0, ord(1), vp); Bstep(k0, ord(2), vp); }
+            if (DO_B) {
+                Bstep(k0, 1, vp);
+                if (LW && CS) ldpair(k0, 2, cA);
+                Bstep(k0, 2, vp);
+            }
             if (DO_C) C2();
-            if (DO_B) { Bstep(k0, ord(3), vp); Bstep(k0, ord(4), vp); }
+            if (DO_B) {
+                Bstep(k0, 3, vp);
+                if (LW && CS) ldpair(k0, 3, cB);
+                Bstep(k0, 4, vp);
+            }
             if (DO_C) C3();
-            if (DO_B) Bstep(k0, ord(5), vp);
+            if (DO_B) {
+                Bstep(k0, 5, vp);
+                if (LW && CS && knext >= 0) ldpair(knext, 0, cA);
+            }
             if (DO_C) C4();
-            if (DO_B) { Bstep(k0, ord(6), vp); Bstep(k0, ord(7), vp); }
+            if (DO_B) {
+                Bstep(k0, 6, vp);
+                Bstep(k0, 7, vp);
+                if (LW && CS && knext >= 0) ldpair(knext, 1, cB);
+            }
             if (DO_C) {
                 C5();
                 Cstore(k0 - kstep);
             }
             if (DO_B) {
+                if constexpr (TM) {
+                    if (more) tmem::wait_ld<NW>(tnw);
+                    tmem::unpack<kU>(tnw, tR);
+                } else {
 #pragma unroll
-                for (int u = 0; u < kU; ++u) {
-                    v[u] = vp[u];
-                    tR[u] = tn8[u];
+                    for (int u = 0; u < kU; ++u) tR[u] = tn8[u];
                 }
+#pragma unroll
+                for (int u = 0; u < kU; ++u) v[u] = vp[u];
                 ccur = cnext;
             }
         };
-#pragma unroll
         if (next_src) prefetch_pass<Real, MM>(!UP, Lp, next_src, lv, fd);
-        for (int u = 0; u < kU; ++u) tR[u] = tsl[(kfirst + u) * 32];
-        if (LW) ccur = crow[kfirst];
+        if constexpr (TM) {
+            tmem::ld<NW>(tst.taddr + (uint32_t)(kfirst * WPR), tnw);
+            tmem::wait_ld<NW>(tnw);
+            tmem::unpack<kU>(tnw, tR);
+        } else {
+#pragma unroll
+            for (int u = 0; u < kU; ++u) tR[u] = tsl[(kfirst + u) * 32];
+        }
+        if (LW && !CS) ccur = crow[kfirst];
+        ldpair(kfirst, 0, cA);
+        ldpair(kfirst, 1, cB);
         iter(std::true_type{}, std::false_type{}, kfirst);
         if (UP) {
             for (int k0 = Lp - 2 * kU; k0 >= 0; k0 -= kU) iter(std::true_type{}, std::true_type{}, k0);
@@ -569,38 +718,43 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
     }
 }
 
-template <typename Real, int MM, bool FRESH>
+template <typename Real, int MM, bool FRESH, int V>
 __device__ __forceinline__ void dispatch_pass(const bool lw, const bool up, const int lane, const int nl, const int Lp,
                                               const Real wF, const Real wR, const Real bs, const Real bg,
                                               const void *src_lane, const void *next_src, PassFeed<Real, MM> &fd,
-                                              const LevelView<Real> &lv, Real *tsl, double *bacc_up, double *bacc_dn,
+                                              const LevelView<Real> &lv, const TStore<Real> tst, double *bacc_up, double *bacc_dn,
                                               const Real *coef) {
-    // coefficient rows of a band: [0] dn_last, [1] dn_gen, [2] up_first, [3] up_gen
+    // coefficient rows of a band: [0] dn_last, [1] dn_gen, [2] up_first, [3] up_gen.  The value of layer k
+    // of a downward pass belongs to interface k + 1: the plain accumulators are indexed by interface, the
+    // partial-sum accumulators (kVarPartial) by layer.
+    double *const dn = (V & kVarPartial) ? bacc_dn : bacc_dn + 1;
     if (lw) {
         if (up)
-            sweep_pass<Real, MM, true, true, FRESH>(lane, nl, Lp, wF, wR, bg, src_lane, next_src, fd, lv, tsl, bacc_up, coef + 2 * Lp, coef + 3 * Lp);
+            sweep_pass<Real, MM, true, true, FRESH, V>(lane, nl, Lp, wF, wR, bg, src_lane, next_src, fd, lv, tst, bacc_up, coef + 2 * Lp, coef + 3 * Lp);
         else
-            sweep_pass<Real, MM, true, false, FRESH>(lane, nl, Lp, wF, wR, bs, src_lane, next_src, fd, lv, tsl, bacc_dn + 1, coef, coef + Lp);
+            sweep_pass<Real, MM, true, false, FRESH, V>(lane, nl, Lp, wF, wR, bs, src_lane, next_src, fd, lv, tst, dn, coef, coef + Lp);
     } else {
         if (up)
-            sweep_pass<Real, MM, false, true, FRESH>(lane, nl, Lp, wF, wR, bg, src_lane, next_src, fd, lv, tsl, bacc_up, coef, coef);
+            sweep_pass<Real, MM, false, true, FRESH, V>(lane, nl, Lp, wF, wR, bg, src_lane, next_src, fd, lv, tst, bacc_up, coef, coef);
         else
-            sweep_pass<Real, MM, false, false, FRESH>(lane, nl, Lp, wF, wR, bs, src_lane, next_src, fd, lv, tsl, bacc_dn + 1, coef, coef);
+            sweep_pass<Real, MM, false, false, FRESH, V>(lane, nl, Lp, wF, wR, bs, src_lane, next_src, fd, lv, tst, dn, coef, coef);
     }
 }
 
 // MM = number of molecules of the table-fused path (compile-time so the prefetched table values
 // live in registers); MM = 0 selects the resident-tau path.  Persistent CTAs: task = (column, c)
 // with c < ctas_per_col; warp w of the CTA sweeps part c * W + w of the column.
-template <typename Real, int MM>
+template <typename Real, int MM, int V = 0>
 __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr bool FUSED = MM > 0;
     constexpr int MR = MM > 0 ? MM : 1;
+    constexpr bool TM = (V & kVarTmem) != 0, CS = (V & kVarCoefSmem) != 0, PA = (V & kVarPartial) != 0;
+    constexpr int WPR = sizeof(Real) / 4, NW = kU * WPR;
     const int tid = threadIdx.x, nthr = blockDim.x, W = nthr >> 5, warp = tid >> 5, lane = tid & 31;
     const int L = a.L, nl = a.L - 1, Lp = padded_layers(a.L), LS = Lp + kU, C = a.ctas_per_col;
 
-    const CtaSmem<Real, MM> lay(L);
+    const CtaSmem<Real, MM, V> lay(L);
     unsigned *lev_offdn = (unsigned *)(smem_raw + lay.off_offdn);
     unsigned *lev_offup = (unsigned *)(smem_raw + lay.off_offup);
     Real *lev_qg = (Real *)(smem_raw + lay.off_qg);
@@ -608,15 +762,33 @@ __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
     const int lstride = lay.lev_stride;
     unsigned char *wbase = smem_raw + lay.shared_total + (size_t)warp * lay.warp_total;
     double *bacc_up = (double *)(wbase + lay.warp_bacc);
-    double *bacc_dn = bacc_up + LS;
+    double *bacc_dn = bacc_up + (PA ? Lp * kPartialLanes : LS);
+    const int n_bacc = PA ? 2 * Lp * kPartialLanes : 2 * LS;      // accumulator doubles per warp
+    Real *cw = (Real *)(wbase + lay.warp_coef);                   // staged coefficient rows (kVarCoefSmem)
     Real *ts = (Real *)(wbase + lay.warp_ts);
     double *sacc = (double *)(smem_raw + lay.shared_total + lay.warp_bacc);   // warp 0's accumulators, free in the epilogue
     Real *coef_cta = a.coefbuf + (size_t)blockIdx.x * a.B * 4 * Lp;
     const LevelView<Real> lv{lev_offdn, lev_offup, lev_qg, lstride, hdp};
 
     for (int k = tid; k < Lp; k += nthr) hdp[k] = k < nl ? (Real)a.hdP[k] : Real(0);
-    for (int i = lane; i < 2 * LS; i += 32) bacc_up[i] = 0.0;
-    for (int i = lane; i < Lp * 32; i += 32) ts[i] = Real(0);   // the first replay of a run reads it with weight 0
+    for (int i = lane; i < n_bacc; i += 32) bacc_up[i] = 0.0;
+    // The t-store: the first replay of a run reads it with weight 0, so it has to hold finite numbers.
+    __shared__ uint32_t s_tmem_base;
+    TStore<Real> tst{ts + lane, 0u};
+    if constexpr (TM) {
+        if (warp == 0) tmem::acquire(&s_tmem_base, (uint32_t)a.tmem_cols);
+        tmem::fence_before_sync();
+        __syncthreads();
+        tmem::fence_after_sync();
+        tst.taddr = tmem::address(s_tmem_base, warp, (warp >> 2) * a.tmem_cpw);
+        uint32_t zero[NW];
+#pragma unroll
+        for (int i = 0; i < NW; ++i) zero[i] = 0u;
+        for (int k0 = 0; k0 < Lp; k0 += kU) tmem::st<NW>(tst.taddr + (uint32_t)(k0 * WPR), zero);
+        tmem::wait_st();
+    } else {
+        for (int i = lane; i < Lp * 32; i += 32) ts[i] = Real(0);
+    }
 
     // Tasks are handed out through a global counter: SMs differ a little in speed (L2 distance,
     // table rows hit), and a static split would leave the fast ones idle at the end.
@@ -731,33 +903,64 @@ __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
             const Real bg = (Real)(M_PI * planck_wavenumber(a.pc, c, Tg));                   // :638
             const Real bs = (Real)(M_PI * planck_wavenumber(a.pc, c, a.T_star) * solar);     // :640-642
             const Real *coef = coef_cta + (size_t)j * 4 * Lp;
-            if (a.seg_c0[s] == 0 && lane == 0) {   // boundary terms: Trans(i,i) = sum of the nu-weights
-                bacc_up[L - 1] += (double)bg * a.band_sumw[j];
-                bacc_dn[0] += (double)bs * a.band_sumw[j];
+            if constexpr (CS) {          // stage the band's four coefficient rows in this warp's shared memory
+                if (lw) {
+                    for (int i = lane; i < 4 * Lp; i += 32) cw[i] = coef[i];
+                    __syncwarp();
+                }
+                coef = cw;
+            }
+            // boundary terms: Trans(i,i) = sum of the nu-weights
+            const bool first_chain = a.seg_c0[s] == 0;
+            const double bnd_up = first_chain ? (double)bg * a.band_sumw[j] : 0.0;
+            const double bnd_dn = first_chain ? (double)bs * a.band_sumw[j] : 0.0;
+            if (!PA && first_chain && lane == 0) {
+                bacc_up[L - 1] += bnd_up;
+                bacc_dn[0] += bnd_dn;
             }
             Real wR = Real(0);
             for (; s < e; ++s) {
                 const Real wF = wN;
                 const void *src_lane = srcN;
                 if (s + 1 < s1) seg_params(s + 1, wN, srcN);
-                dispatch_pass<Real, MM, true>(lw, up, lane, nl, Lp, wF, wR, bs, bg, src_lane, s + 1 < e ? srcN : nullptr, fd, lv,
-                                              ts + lane, bacc_up, bacc_dn, coef);
+                dispatch_pass<Real, MM, true, V>(lw, up, lane, nl, Lp, wF, wR, bs, bg, src_lane, s + 1 < e ? srcN : nullptr, fd, lv,
+                                                 tst, bacc_up, bacc_dn, coef);
                 wR = wF;
                 up = !up;
             }
-            dispatch_pass<Real, MM, false>(lw, up, lane, nl, Lp, Real(0), wR, bs, bg, nullptr, s < s1 ? srcN : nullptr, fd, lv,
-                                           ts + lane, bacc_up, bacc_dn, coef);
+            dispatch_pass<Real, MM, false, V>(lw, up, lane, nl, Lp, Real(0), wR, bs, bg, nullptr, s < s1 ? srcN : nullptr, fd, lv,
+                                              tst, bacc_up, bacc_dn, coef);
             up = !up;
             // ---- partial band sums of this (warp, band) run -> scratch slot ---------------------------
             __syncwarp();
             double *o = a.scratch + ((region * a.n_slots + slot) * 2) * (int64_t)L;
-            for (int i = lane; i < L; i += 32) {
-                o[i] = bacc_up[i];
-                o[L + i] = bacc_dn[i];
+            if constexpr (PA) {
+                // accumulators [layer / 2][lane & 7][layer % 2]: add the eight partials in order; an upward
+                // layer k is interface k, a downward layer k interface k + 1
+                for (int i = lane; i < L; i += 32) {
+                    double su = i == L - 1 ? bnd_up : 0.0, sd = i == 0 ? bnd_dn : 0.0;
+                    if (i < nl) {
+                        const double *pu = bacc_up + (i >> 1) * (2 * kPartialLanes) + (i & 1);
+#pragma unroll
+                        for (int c = 0; c < kPartialLanes; ++c) su += pu[2 * c];
+                    }
+                    if (i >= 1) {
+                        const double *pd = bacc_dn + ((i - 1) >> 1) * (2 * kPartialLanes) + ((i - 1) & 1);
+#pragma unroll
+                        for (int c = 0; c < kPartialLanes; ++c) sd += pd[2 * c];
+                    }
+                    o[i] = su;
+                    o[L + i] = sd;
+                }
+            } else {
+                for (int i = lane; i < L; i += 32) {
+                    o[i] = bacc_up[i];
+                    o[L + i] = bacc_dn[i];
+                }
             }
             ++slot;
             __syncwarp();
-            for (int i = lane; i < 2 * LS; i += 32) bacc_up[i] = 0.0;
+            for (int i = lane; i < n_bacc / 2; i += 32) reinterpret_cast<double2 *>(bacc_up)[i] = make_double2(0.0, 0.0);
             __syncwarp();
         }
         const bool dbg_here = a.dbg && n_done == (int)(a.n_tasks / gridDim.x / 2) && blockIdx.x == 0 && lane == 0;
@@ -810,6 +1013,11 @@ __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
         __syncthreads();
         for (int idx = tid; idx < 2 * L; idx += nthr) sacc[idx] = 0.0;
         if (dbg_here) a.dbg[48 + warp] = clock64() - t_task0;
+    }
+    if constexpr (TM) {      // every warp left the task loop behind the same barrier: nobody uses TMEM any more
+        tmem::fence_before_sync();
+        __syncthreads();
+        if (warp == 0) tmem::release(s_tmem_base, (uint32_t)a.tmem_cols);
     }
 }
 

@@ -1,0 +1,107 @@
+// Tensor memory (TMEM, 256 KB per SM on sm_100a) used as per-lane private scratch.
+//
+// TMEM is 128 lanes x 512 columns of 32 bits; warp w of a CTA reaches lanes 32 (w % 4) .. + 31, and
+// with the 32x32b access shape thread t of the warp reads / writes consecutive columns of lane
+// 32 (w % 4) + t.  That is exactly the access pattern of the flux kernel's t-store (every chain = lane
+// parks its own layer transmissivities and replays them in the opposite direction), so the t-store
+// can live here instead of in shared memory: one LDTM / STTM moves a block of kU values per lane.
+#pragma once
+#include <cstdint>
+
+namespace cmb {
+namespace tmem {
+
+// One warp allocates n_cols (power of two, 32..512) columns for the CTA; the base address lands
+// in *slot (shared memory).  The same warp frees them with release().
+__device__ __forceinline__ void acquire(uint32_t *slot, uint32_t n_cols) {
+    const uint32_t dst = (uint32_t)__cvta_generic_to_shared(slot);
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst), "r"(n_cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void release(uint32_t base, uint32_t n_cols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(base), "r"(n_cols) : "memory");
+}
+__device__ __forceinline__ void fence_before_sync() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_after_sync() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// Address of column c in the lane quarter of warp `warp`.
+__device__ __forceinline__ uint32_t address(uint32_t base, int warp, int col) {
+    return base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)col;
+}
+
+// Block load / store of NW consecutive columns per lane (NW = 8 or 16).  The loaded registers are
+// only valid after wait_ld(), which takes them as in-out operands so that no use is scheduled earlier.
+template <int NW>
+__device__ __forceinline__ void ld(uint32_t addr, uint32_t (&r)[NW]) {
+    static_assert(NW == 8 || NW == 16, "block of 8 or 16 columns");
+    if constexpr (NW == 16) {
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                     : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                       "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                     : "r"(addr));
+    } else {
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                     : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                     : "r"(addr));
+    }
+}
+template <int NW>
+__device__ __forceinline__ void wait_ld(uint32_t (&r)[NW]) {
+    if constexpr (NW == 16) {
+        asm volatile("tcgen05.wait::ld.sync.aligned;"
+                     : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                       "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15])
+                     :
+                     : "memory");
+    } else {
+        asm volatile("tcgen05.wait::ld.sync.aligned;"
+                     : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7])
+                     :
+                     : "memory");
+    }
+}
+template <int NW>
+__device__ __forceinline__ void st(uint32_t addr, const uint32_t (&r)[NW]) {
+    static_assert(NW == 8 || NW == 16, "block of 8 or 16 columns");
+    if constexpr (NW == 16) {
+        asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+                     :
+                     : "r"(addr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+                       "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+                     : "memory");
+    } else {
+        asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+                     :
+                     : "r"(addr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+                     : "memory");
+    }
+}
+
+// kU reals <-> 32-bit words (register renames, no instructions).
+template <int N>
+__device__ __forceinline__ void pack(const double (&v)[N], uint32_t (&w)[2 * N]) {
+#pragma unroll
+    for (int u = 0; u < N; ++u) {
+        w[2 * u] = (uint32_t)__double2loint(v[u]);
+        w[2 * u + 1] = (uint32_t)__double2hiint(v[u]);
+    }
+}
+template <int N>
+__device__ __forceinline__ void unpack(const uint32_t (&w)[2 * N], double (&v)[N]) {
+#pragma unroll
+    for (int u = 0; u < N; ++u) v[u] = __hiloint2double((int)w[2 * u + 1], (int)w[2 * u]);
+}
+template <int N>
+__device__ __forceinline__ void pack(const float (&v)[N], uint32_t (&w)[N]) {
+#pragma unroll
+    for (int u = 0; u < N; ++u) w[u] = __float_as_uint(v[u]);
+}
+template <int N>
+__device__ __forceinline__ void unpack(const uint32_t (&w)[N], float (&v)[N]) {
+#pragma unroll
+    for (int u = 0; u < N; ++u) v[u] = __uint_as_float(w[u]);
+}
+
+}  // namespace tmem
+}  // namespace cmb
