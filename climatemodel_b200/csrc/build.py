@@ -38,7 +38,11 @@ def stale():
 def build(force=False, verbose=False):
     if not force and not stale():
         return LIB
-    cmd = [nvcc_path()] + NVCC_FLAGS + (['-Xptxas', '-v'] if verbose else []) + \
+    extra = []
+    experiments = [v for v in os.environ.get('CMB200_EXPERIMENTS', '').split(',') if v.strip()]
+    if experiments:      # extra flux kernel variants for tools/ab_flux_variants.py (flux.cu)
+        extra.append('-DCMB_FLUX_EXPERIMENTS(X)=' + ' '.join('X(%d)' % int(v) for v in experiments))
+    cmd = [nvcc_path()] + NVCC_FLAGS + extra + (['-Xptxas', '-v'] if verbose else []) + \
           ['-o', LIB, os.path.join(HERE, 'unity.cu')]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:

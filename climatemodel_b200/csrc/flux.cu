@@ -107,38 +107,55 @@ static int ensure_partition(cmb200_plan *p, int64_t n_col, int W, int resident_c
 
 // Warps per CTA of kernel variant V for L interfaces: bounded by shared memory (t-store, accumulators,
 // coefficient rows) and, for the tensor-memory t-store, by the 512 columns of a lane quarter shared
-// by the warps w, w + 4, ...  0 = the variant cannot run this L.
+// by the warps w, w + 4, ...  0 = the variant cannot run this L.  tm_rows = layers of a warp's t-store
+// kept in tensor memory (kVarMixed: as many whole blocks as a third of a lane quarter holds).
 template <typename Real, int MM, int V>
-static int variant_warps(int L, int max_smem, int *tmem_cpw, int *tmem_cols) {
-    const CtaSmem<Real, MM, V> lay(L);
-    int W = (size_t)max_smem > lay.shared_total
-                ? (int)std::min<size_t>(8, ((size_t)max_smem - lay.shared_total) / lay.warp_total)
-                : 0;
-    *tmem_cpw = *tmem_cols = 0;
+static int variant_warps(int L, int max_smem, int *tmem_cpw, int *tmem_cols, int *tm_rows) {
+    const int Lp = padded_layers(L), wpr = (int)(sizeof(Real) / 4);
+    *tmem_cpw = *tmem_cols = *tm_rows = 0;
+    int ts_rows = -1, most = 8;
     if (V & kVarTmem) {
-        const int cpw = padded_layers(L) * (int)(sizeof(Real) / 4);
-        const int per_quarter = std::min(2, 512 / cpw);
-        W = std::min(W, 4 * per_quarter) / 4 * 4;      // whole lane quarters
+        int per_quarter;
+        if (V & kVarMixed) {
+            per_quarter = 3;
+            *tm_rows = std::min(Lp, (512 / per_quarter / wpr) / kU * kU);
+            ts_rows = Lp - *tm_rows;
+        } else {
+            per_quarter = std::min(2, 512 / (Lp * wpr));
+            *tm_rows = Lp;
+        }
+        most = 4 * per_quarter;
+        const int cpw = *tm_rows * wpr;
         int cols = 32;
         while (cols < per_quarter * cpw) cols *= 2;
         *tmem_cpw = cpw;
         *tmem_cols = cols;
     }
+    const CtaSmem<Real, MM, V> lay(L, ts_rows);
+    int W = (size_t)max_smem > lay.shared_total
+                ? (int)std::min<size_t>(most, ((size_t)max_smem - lay.shared_total) / lay.warp_total)
+                : 0;
+    if (V & kVarTmem) W = W / 4 * 4;                     // whole lane quarters
+    if ((V & kVarMixed) && W < 12) W = 0;                // the point of the variant is the twelve warps
     return W;
 }
 
-// Default kernel variant (see flux_kernels.cuh); CMB200_FLUX_VARIANT overrides it for experiments.
-constexpr int kDefaultVariant = 0;
+// Kernel variants (flux_kernels.cuh).  Every (precision, molecule count) has the plain kernel (0) and
+// the default one; further variants are experiments, compiled for FP64 with 0 or 2 molecules only
+// when the build names them (CMB200_EXPERIMENTS="17,21" python -m climatemodel_b200.csrc.build) and
+// selected at run time with CMB200_FLUX_VARIANT (tools/ab_flux_variants.py).
+constexpr int kDefaultVariant = kVarTmem | kVarCoefSmem;
+#ifndef CMB_FLUX_EXPERIMENTS
+#define CMB_FLUX_EXPERIMENTS(X)
+#endif
 static int flux_variant() {
     const char *e = getenv("CMB200_FLUX_VARIANT");
-    const int v = e && *e ? atoi(e) : kDefaultVariant;
-    return (v == 1 || v == 3 || v == 7) ? v : 0;
+    return e && *e ? atoi(e) : kDefaultVariant;
 }
 
 template <typename Real, int MM, int V>
 static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *Tint, cudaStream_t s) {
     const int L = p->L, Lp = padded_layers(L);
-    const CtaSmem<Real, MM, V> lay(L);
     const double span = MM > 0 ? (double)MM * L * p->nT_pad * (double)p->pitch * sizeof(Real) / 16.0 : (double)L * (double)p->N;
     if (span >= 4294967296.0) {
         set_error("table / tau rows exceed the 32-bit row offsets of the flux kernel (%.3g units)", span);
@@ -146,12 +163,13 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     }
     int max_smem = 0;
     CMB_CUDA(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, p->device));
-    int tmem_cpw = 0, tmem_cols = 0;
-    const int W = variant_warps<Real, MM, V>(L, max_smem, &tmem_cpw, &tmem_cols);
+    int tmem_cpw = 0, tmem_cols = 0, tm_rows = 0;
+    const int W = variant_warps<Real, MM, V>(L, max_smem, &tmem_cpw, &tmem_cols, &tm_rows);
     if constexpr (V != 0) {      // the variant has to offer at least the warps of the plain kernel, else that one runs
-        int c0, c1;
-        if (W < variant_warps<Real, MM, 0>(L, max_smem, &c0, &c1)) return launch_flux<Real, MM, 0>(p, io, Tint, s);
+        int c0, c1, c2;
+        if (W < variant_warps<Real, MM, 0>(L, max_smem, &c0, &c1, &c2)) return launch_flux<Real, MM, 0>(p, io, Tint, s);
     }
+    const CtaSmem<Real, MM, V> lay(L, (V & kVarMixed) ? Lp - tm_rows : -1);
     if (W < 1) {
         set_error("%d levels need %zu bytes of shared memory per CTA; the device offers %d", L, lay.total(1), max_smem);
         return CMB200_ERR_LIMIT;
@@ -255,6 +273,7 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     }
     a.tmem_cpw = tmem_cpw;
     a.tmem_cols = tmem_cols;
+    a.tm_rows = tm_rows;
     flux_kernel<Real, MM, V><<<(unsigned)grid, W * 32, smem, s>>>(a);
     CMB_LAUNCHED();
     if (debug_timing) {   // per-warp sweep cycles of CTA 0's first column next to what the partition gave each warp
@@ -288,9 +307,26 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     return CMB200_OK;
 }
 
-__global__ void exp_neg_test_kernel(const double *__restrict__ x, int64_t n, double *__restrict__ out) {
-    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-    if (i < n) out[i] = exp_neg(x[i]);
+__global__ void exp_neg_test_kernel(const double *__restrict__ x, int64_t n, double *__restrict__ out, bool table) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    const double xi = x[i < n ? i : n - 1];          // whole warps: the table routine shuffles
+    const double r = table ? exp_neg_table(xi, kExpTab[threadIdx.x & 31]) : exp_neg(xi);
+    if (i < n) out[i] = r;
+}
+
+template <typename Real, int MM>
+static int launch_flux_variant(int variant, cmb200_plan *plan, const cmb200_flux_io *io, const double *Tint, cudaStream_t s) {
+    if constexpr (std::is_same<Real, double>::value && (MM == 0 || MM == 2)) {
+#define CMB_FLUX_X(V_) \
+    case V_: return launch_flux<Real, MM, V_>(plan, io, Tint, s);
+        switch (variant) {
+            CMB_FLUX_EXPERIMENTS(CMB_FLUX_X)
+            default: break;
+        }
+#undef CMB_FLUX_X
+    }
+    if (variant == 0) return launch_flux<Real, MM, 0>(plan, io, Tint, s);
+    return launch_flux<Real, MM, kDefaultVariant>(plan, io, Tint, s);
 }
 
 static int validate_flux_io(const cmb200_plan *p, const cmb200_flux_io *io) {
@@ -431,14 +467,8 @@ extern "C" int cmb200_flux(cmb200_plan *plan, const cmb200_flux_io *io, void *st
     }
     const int mm = fused ? plan->M : 0;
     const int variant = flux_variant();
-#define CMB_FLUX_CASE(REAL, M_)                                                     \
-    case M_:                                                                        \
-        switch (variant) {                                                          \
-            case 1: return launch_flux<REAL, M_, 1>(plan, io, Tint, s);             \
-            case 3: return launch_flux<REAL, M_, 3>(plan, io, Tint, s);             \
-            case 7: return launch_flux<REAL, M_, 7>(plan, io, Tint, s);             \
-            default: return launch_flux<REAL, M_, 0>(plan, io, Tint, s);            \
-        }
+#define CMB_FLUX_CASE(REAL, M_) \
+    case M_: return launch_flux_variant<REAL, M_>(variant, plan, io, Tint, s);
     if (plan->precision == CMB200_F64) {
         switch (mm) {
             CMB_FLUX_CASE(double, 0)
@@ -618,7 +648,7 @@ extern "C" int cmb200_test_exp_neg_host(const double *x, int64_t n, double *out)
     DevBuf<double> dx, dout;
     CMB_CUDA(dx.upload(x, n));
     CMB_CUDA(dout.alloc(n));
-    exp_neg_test_kernel<<<(unsigned)((n + 255) / 256), 256>>>(dx.p, n, dout.p);
+    exp_neg_test_kernel<<<(unsigned)((n + 255) / 256), 256>>>(dx.p, n, dout.p, (flux_variant() & kVarExpTable) != 0);
     CMB_LAUNCHED();
     CMB_CUDA(cudaMemcpy(out, dout.p, n * sizeof(double), cudaMemcpyDeviceToHost));
     return CMB200_OK;

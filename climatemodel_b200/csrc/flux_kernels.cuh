@@ -63,6 +63,7 @@ struct FluxArgs {
     unsigned long long *task_counter;   // zeroed before the launch
     long long *dbg;            // optional: sweep cycles per warp of CTA 0's first task (CMB200_DEBUG_TIMING)
     int tmem_cols, tmem_cpw;   // TMEM t-store: columns allocated per CTA, columns per warp (V & kVarTmem)
+    int tm_rows;               // layers of a warp's t-store kept in tensor memory (the rest in shared memory)
 };
 
 // Kernel variants (template parameter V, a bit set):
@@ -74,8 +75,20 @@ struct FluxArgs {
 //   kVarPartial   the warp reduction of a block stops after two exchange steps and the four-lane
 //                 partial sums are accumulated in shared memory per (interface, lane & 7); the eight
 //                 partials are added when the (warp, band) run is written out.
-constexpr int kVarTmem = 1, kVarCoefSmem = 2, kVarPartial = 4;
+//   kVarMixed     (with kVarTmem) twelve warps per CTA instead of eight: three warps share a lane quarter
+//                 of tensor memory, so each keeps the first tm_rows layers of its t-store there and the
+//                 rest in shared memory; the kernel is compiled for 384 threads (168 registers).
+//   kVarExpTable  (FP64) exp(-x) = 2^n 2^(j/32) e^r with a 32-entry table of 2^(j/32) held one entry per
+//                 lane and fetched with two shuffles, |r| <= ln2/64 and a degree-6 polynomial: 11 FP64
+//                 instructions per layer instead of 15;
+//   kVarExpRegs   its constants are pinned in registers (a DFMA with a constant-bank operand issues
+//                 every 2.46 cycles instead of every 2, tools/issue_mix_microbench.cu).
+constexpr int kVarTmem = 1, kVarCoefSmem = 2, kVarPartial = 4, kVarMixed = 8, kVarExpTable = 16, kVarExpRegs = 32;
+// Ablation switches for timing experiments only (results are wrong): skip the table loads after the
+// first block, the exp polynomial, the warp reduction, the t-store traffic.
+constexpr int kAblLoads = 64, kAblExp = 128, kAblReduce = 256, kAblTstore = 512;
 constexpr int kPartialLanes = 8;
+constexpr int variant_threads(int V) { return (V & kVarMixed) ? 384 : 256; }
 
 constexpr int kU = 8;          // layers per block of a pass (instruction-level parallelism)
 
@@ -136,9 +149,11 @@ template <typename Real, int MM, int V = 0>
 struct CtaSmem {
     size_t off_offdn, off_offup, off_qg, off_hdp, shared_total, warp_bacc, warp_coef, warp_ts, warp_total;
     int lev_stride;
-    __host__ __device__ CtaSmem(int L) {
+    // ts_rows: layers of the t-store a warp keeps in shared memory (-1: all of them, or none with kVarTmem)
+    __host__ __device__ CtaSmem(int L, int ts_rows = -1) {
         auto up16 = [](size_t x) { return (x + 15) & ~(size_t)15; };
         const int Lp = padded_layers(L), MR = MM > 0 ? MM : 1;
+        if (ts_rows < 0) ts_rows = (V & kVarTmem) ? 0 : Lp;
         lev_stride = Lp + kU;
         size_t b = 0;
         off_offdn = b;
@@ -156,7 +171,7 @@ struct CtaSmem {
         warp_coef = up16((V & kVarPartial) ? (size_t)2 * Lp * kPartialLanes * sizeof(double)
                                            : (size_t)2 * (Lp + kU) * sizeof(double));
         warp_ts = up16(warp_coef + ((V & kVarCoefSmem) ? (size_t)4 * Lp * sizeof(Real) : 0));
-        warp_total = up16(warp_ts + ((V & kVarTmem) ? 0 : (size_t)Lp * 32 * sizeof(Real)));
+        warp_total = up16(warp_ts + (size_t)ts_rows * 32 * sizeof(Real));
     }
     __host__ __device__ size_t total(int warps) const { return shared_total + warp_total * warps; }
 };
@@ -165,8 +180,9 @@ struct CtaSmem {
 // tensor-memory address (lane quarter and first column of the warp).
 template <typename Real>
 struct TStore {
-    Real *lane;
-    uint32_t taddr;
+    Real *lane;        // shared-memory row of layer k: lane + (k - tm_rows) * 32
+    uint32_t taddr;    // tensor-memory column of layer k: taddr + k * (sizeof(Real) / 4)
+    int tm_rows;       // kVarMixed: layers [0, tm_rows) live in tensor memory, the others in shared memory
 };
 
 // exp(-x) for the layer transmissivity.  FP64: n = rint(-x log2 e), r = -x - n ln2 (two-term
@@ -197,6 +213,42 @@ __device__ __forceinline__ double exp_neg(double x) {
     for (int i = 1; i <= 10; ++i) p = fma(p, r, kExpC[i]);
     p = fma(p, r, kExpC[10]);
     return __hiloint2double(__double2hiint(p) + (n << 20), __double2loint(p));
+}
+// Table variant (kVarExpTable): n' = rint(-x 32/ln2) = 32 n + j, r = -x - n' ln2/32 (two-term, the high
+// part has 37 bits so that n' * hi is exact), e^r - 1 = r + r^2 g(r) with g of degree 4 (truncation
+// 3.5e-18), t = T_j + T_j (r + r^2 g), T_j = 2^(j/32) correctly rounded; < 1 ulp overall.
+// kExpT: [0] 32/ln2, [1] 1.5 * 2^52, [2] -hi, [3] -lo, [4..8] 1/720, 1/120, 1/24, 1/6, 1/2.
+__constant__ double kExpT[9] = {0x1.71547652b82fep+5, 6755399441055744.0, -0x1.62e42fefa0000p-6, -0x1.cf79abc9e3b3ap-45,
+                                1.0 / 720.0, 1.0 / 120.0, 1.0 / 24.0, 1.0 / 6.0, 0.5};
+__constant__ double kExpTab[32] = {
+    0x1.0000000000000p+0, 0x1.059b0d3158574p+0, 0x1.0b5586cf9890fp+0, 0x1.11301d0125b51p+0,
+    0x1.172b83c7d517bp+0, 0x1.1d4873168b9aap+0, 0x1.2387a6e756238p+0, 0x1.29e9df51fdee1p+0,
+    0x1.306fe0a31b715p+0, 0x1.371a7373aa9cbp+0, 0x1.3dea64c123422p+0, 0x1.44e086061892dp+0,
+    0x1.4bfdad5362a27p+0, 0x1.5342b569d4f82p+0, 0x1.5ab07dd485429p+0, 0x1.6247eb03a5585p+0,
+    0x1.6a09e667f3bcdp+0, 0x1.71f75e8ec5f74p+0, 0x1.7a11473eb0187p+0, 0x1.82589994cce13p+0,
+    0x1.8ace5422aa0dbp+0, 0x1.93737b0cdc5e5p+0, 0x1.9c49182a3f090p+0, 0x1.a5503b23e255dp+0,
+    0x1.ae89f995ad3adp+0, 0x1.b7f76f2fb5e47p+0, 0x1.c199bdd85529cp+0, 0x1.cb720dcef9069p+0,
+    0x1.d5818dcfba487p+0, 0x1.dfc97337b9b5fp+0, 0x1.ea4afa2a490dap+0, 0x1.f50765b6e4540p+0};
+__device__ __forceinline__ double shfl_f64(double v, int src) {
+    const int lo = __shfl_sync(0xffffffffu, __double2loint(v), src), hi = __shfl_sync(0xffffffffu, __double2hiint(v), src);
+    return __hiloint2double(hi, lo);
+}
+// All 32 lanes of the warp must call this together; tabT = kExpTab[lane].
+__device__ __forceinline__ double exp_neg_table(double x, double tabT) {
+    x = clamp_thickness(x);
+    double tn = fma(-x, kExpT[0], kExpT[1]);
+    const int np = __double2loint(tn);
+    tn -= kExpT[1];
+    const double Tj = shfl_f64(tabT, np & 31);
+    double r = fma(tn, kExpT[2], -x);
+    r = fma(tn, kExpT[3], r);
+    const double r2 = r * r;
+    double g = fma(kExpT[4], r, kExpT[5]);
+    g = fma(g, r, kExpT[6]);
+    g = fma(g, r, kExpT[7]);
+    g = fma(g, r, kExpT[8]);
+    const double t = fma(Tj, fma(r2, g, r), Tj);
+    return __hiloint2double(__double2hiint(t) + ((np >> 5) << 20), __double2loint(t));
 }
 // The same for kU values at once, written step-by-step across the values so that the kU
 // independent dependency chains are adjacent in program order and the FP64 pipe stays busy.
@@ -318,11 +370,13 @@ template <typename Real, int MM, bool LW, bool UP, bool FRESH, int V>
 __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const int Lp, const Real wF, const Real wR,
                                            const Real b0, const void *src_lane, const void *next_src,
                                            PassFeed<Real, MM> &fd, const LevelView<Real> lv, const TStore<Real> tst,
-                                           double *bacc, const Real *coefL, const Real *coefG) {
+                                           double *bacc, const Real *coefL, const Real *coefG, const double tabT) {
     constexpr bool FUSED = MM > 0;
     constexpr int MR = MM > 0 ? MM : 1;
     constexpr bool F64 = sizeof(Real) == 8;
     constexpr bool TM = (V & kVarTmem) != 0, CS = (V & kVarCoefSmem) != 0, PA = (V & kVarPartial) != 0;
+    constexpr bool MIX = TM && (V & kVarMixed) != 0;
+    constexpr bool XT = F64 && (V & kVarExpTable) != 0, XR = XT && (V & kVarExpRegs) != 0;
     constexpr int WPR = sizeof(Real) / 4, NW = kU * WPR;   // 32-bit words per value / per block and lane
     using Src = typename std::conditional<FUSED, Real, double>::type;
     const char *src_bytes = (const char *)src_lane;
@@ -332,11 +386,40 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
     const int ridx = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
     const bool rlane = (lane & 3) == 0;
     const int kfirst = UP ? Lp - kU : 0, kstep = UP ? -kU : kU;
-    Real *const tsl = tst.lane;
+    Real *const tsl = MIX ? tst.lane - tst.tm_rows * 32 : tst.lane;   // layer k sits at tsl[k * 32]
+    // Tensor-memory modes: one block (kU layers) of the t-store <-> NW words per lane.  kVarMixed:
+    // blocks below tm_rows are in tensor memory, the others in shared memory (warp-uniform branch).
+    auto ts_fetch = [&](int k0, uint32_t(&w)[NW]) {
+        if constexpr ((V & kAblTstore) != 0) return;
+        if (!MIX || k0 < tst.tm_rows) {
+            tmem::ld<NW>(tst.taddr + (uint32_t)(k0 * WPR), w);
+        } else {
+            Real tmp[kU];
+#pragma unroll
+            for (int u = 0; u < kU; ++u) tmp[u] = tsl[(k0 + u) * 32];
+            tmem::pack<kU>(tmp, w);
+        }
+    };
+    auto ts_park = [&](int k0, const Real(&t)[kU]) {
+        if constexpr ((V & kAblTstore) != 0) return;
+        if (!MIX || k0 < tst.tm_rows) {
+            uint32_t tw[NW];
+            tmem::pack<kU>(t, tw);
+            tmem::st<NW>(tst.taddr + (uint32_t)(k0 * WPR), tw);
+        } else {
+#pragma unroll
+            for (int u = 0; u < kU; ++u) tsl[(k0 + u) * 32] = t[u];
+        }
+    };
 
     // ---- warp reduction of v[0..7], split into five steps for the interleave ----------------------
     Real v[kU], a4[4], a2[2], c1;
     auto C1 = [&]() {
+        if constexpr ((V & kAblReduce) != 0) {
+            a4[0] = v[0] + v[1] + v[2] + v[3] + v[4] + v[5] + v[6] + v[7];
+            a4[1] = a4[2] = a4[3] = a4[0];
+            return;
+        }
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const Real keep = h4 ? v[i + 4] : v[i], send = h4 ? v[i] : v[i + 4];
@@ -344,6 +427,10 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
         }
     };
     auto C2 = [&]() {
+        if constexpr ((V & kAblReduce) != 0) {
+            a2[0] = a2[1] = a4[0];
+            return;
+        }
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
             const Real keep = h3 ? a4[i + 2] : a4[i], send = h3 ? a4[i] : a4[i + 2];
@@ -351,16 +438,18 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
         }
     };
     auto C3 = [&]() {
-        if constexpr (!PA) {
+        if constexpr ((V & kAblReduce) != 0) {
+            c1 = a2[0];
+        } else if constexpr (!PA) {
             const Real keep = h2 ? a2[1] : a2[0], send = h2 ? a2[0] : a2[1];
             c1 = keep + __shfl_xor_sync(full, send, 4);
         }
     };
     auto C4 = [&]() {
-        if constexpr (!PA) c1 += __shfl_xor_sync(full, c1, 2);
+        if constexpr (!PA && !(V & kAblReduce)) c1 += __shfl_xor_sync(full, c1, 2);
     };
     auto C5 = [&]() {
-        if constexpr (!PA) c1 += __shfl_xor_sync(full, c1, 1);
+        if constexpr (!PA && !(V & kAblReduce)) c1 += __shfl_xor_sync(full, c1, 1);
     };
     // band accumulator of the reduced block: fetched early so that the read latency is off the tail.
     // Partial mode: after C2 this lane holds the sums over lanes {l, l^8, l^16, l^24} of the two
@@ -452,6 +541,16 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
         }
     };
 
+    // constants of the table exp: constant-bank operands, or pinned in registers (kVarExpRegs)
+    double xc[9];
+    if constexpr (XT) {
+#pragma unroll
+        for (int i = 0; i < 9; ++i) {
+            xc[i] = kExpT[i];
+            if constexpr (XR) asm volatile("mov.b64 %0, %0;" : "+d"(xc[i]));
+        }
+    }
+
     if constexpr (FRESH) {
         // raw[u][m]: table value (or tau) of the block's loaded interfaces, fetched one block ahead so
         // that the L2 / HBM latency hides behind the previous block's work.
@@ -491,7 +590,7 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
         };
         auto fetch_replay = [&](int k0) {
             if constexpr (TM) {
-                tmem::ld<NW>(tst.taddr + (uint32_t)(k0 * WPR), tRw);
+                ts_fetch(k0, tRw);
             } else {
 #pragma unroll
                 for (int u = 0; u < kU; ++u) tR[u] = tsl[(k0 + u) * 32];
@@ -524,7 +623,8 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
 #pragma unroll
                     for (int u = 0; u < kU; ++u) In[u] = raw[u][0];
                 }
-                if (UP ? k0 >= kU : k0 + kU < Lp) load_block(k0 + kstep);
+                if constexpr (!(V & kAblLoads))
+                    if (UP ? k0 >= kU : k0 + kU < Lp) load_block(k0 + kstep);
                 Real hd[kU];
                 if (FUSED) lds_block(lv.hdp + k0, hd);
 #pragma unroll
@@ -535,7 +635,69 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
                 }
                 Ic = UP ? In[0] : In[kU - 1];
             }
-            if constexpr (F64) {
+            if constexpr (XT) {
+                // exp(-x) with the 2^(j/32) table (exp_neg_table), step by step across the block's layers
+                double tn[kU], r[kU], r2[kU], g[kU], Tj[kU];
+                int nsh[kU];
+                if (DO_A) {
+#pragma unroll
+                    for (int u = 0; u < kU; ++u) {
+                        x[u] = clamp_thickness(x[u]);
+                        tn[u] = fma(-x[u], xc[0], xc[1]);
+                    }
+                }
+                if (DO_B) { Bpair(kb, 0, v, knext); park(kb, 0); park(kb, 1); }
+                if (DO_A) {
+#pragma unroll
+                    for (int u = 0; u < kU; ++u) {
+                        const int np = __double2loint(tn[u]);
+                        tn[u] -= xc[1];
+                        nsh[u] = (np >> 5) << 20;
+                        Tj[u] = shfl_f64(tabT, np & 31);
+                    }
+                }
+                if (DO_B) { Bpair(kb, 1, v, knext); park(kb, 2); park(kb, 3); }
+                if (DO_A) {
+#pragma unroll
+                    for (int u = 0; u < kU; ++u) r[u] = fma(tn[u], xc[2], -x[u]);
+                }
+                if (DO_B) { Bpair(kb, 2, v, knext); park(kb, 4); park(kb, 5); }
+                if (DO_A) {
+#pragma unroll
+                    for (int u = 0; u < kU; ++u) r[u] = fma(tn[u], xc[3], r[u]);
+                }
+                // The reduction of block kb is a chain of five shuffle + add steps (~35 cycles each): it starts
+                // right after the block's last recurrence and its last step waits until the end of the iteration.
+                if (DO_B) { Bpair(kb, 3, v, knext); park(kb, 6); park(kb, 7); C1(); }
+                if (DO_A) fetch_replay(k0);
+                if (DO_A) {
+#pragma unroll
+                    for (int u = 0; u < kU; ++u) {
+                        r2[u] = r[u] * r[u];
+                        g[u] = fma(xc[4], r[u], xc[5]);
+                    }
+#pragma unroll
+                    for (int u = 0; u < kU; ++u) g[u] = fma(g[u], r[u], xc[6]);
+                }
+                if (DO_B) C2();
+                if (DO_A) {
+#pragma unroll
+                    for (int u = 0; u < kU; ++u) g[u] = fma(g[u], r[u], xc[7]);
+#pragma unroll
+                    for (int u = 0; u < kU; ++u) g[u] = fma(g[u], r[u], xc[8]);
+                }
+                if (DO_B) C3();
+                if (DO_A) {
+#pragma unroll
+                    for (int u = 0; u < kU; ++u) g[u] = fma(r2[u], g[u], r[u]);
+#pragma unroll
+                    for (int u = 0; u < kU; ++u) {
+                        const double tt = fma(Tj[u], g[u], Tj[u]);
+                        t[u] = __hiloint2double(__double2hiint(tt) + nsh[u], __double2loint(tt));
+                    }
+                }
+                if (DO_B) C4();
+            } else if constexpr (F64) {
                 double tn[kU], r[kU], p[kU];
                 int n[kU];
                 if (DO_A) {
@@ -570,7 +732,7 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
                 if (DO_A) fetch_replay(k0);
 #pragma unroll
                 for (int i = 1; i <= 10; ++i) {
-                    if (DO_A) {
+                    if (DO_A && !(V & kAblExp)) {
 #pragma unroll
                         for (int u = 0; u < kU; ++u) p[u] = fma(p[u], r[u], kExpC[i]);
                     }
@@ -605,14 +767,12 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
                 if (DO_A) fetch_replay(k0);
                 if (DO_B) { C1(); C2(); C3(); C4(); C5(); }
             }
-            if (DO_B) Cstore(kb);
+            if (DO_B && !XT) Cstore(kb);
             if (DO_A) {
                 if constexpr (TM) {
                     tmem::wait_ld<NW>(tRw);
                     tmem::unpack<kU>(tRw, tR);
-                    uint32_t tw[NW];
-                    tmem::pack<kU>(t, tw);
-                    tmem::st<NW>(tst.taddr + (uint32_t)(k0 * WPR), tw);
+                    ts_park(k0, t);
                 }
 #pragma unroll
                 for (int u = 0; u < kU; ++u) tp[u] = t[u];
@@ -621,6 +781,10 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
                     ldpair(k0, 0, cA);
                     ldpair(k0, 1, cB);
                 }
+            }
+            if (DO_B && XT) {
+                C5();
+                Cstore(kb);
             }
         };
         iter(std::true_type{}, std::false_type{}, kfirst);
@@ -647,7 +811,7 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
             if (DO_C) Cload(k0 - kstep);
             if (more) {
                 if constexpr (TM) {
-                    tmem::ld<NW>(tst.taddr + (uint32_t)((k0 + kstep) * WPR), tnw);
+                    ts_fetch(k0 + kstep, tnw);
                 } else {
 #pragma unroll
                     for (int u = 0; u < kU; ++u) tn8[u] = tsl[(k0 + kstep + u) * 32];
@@ -697,7 +861,7 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
         };
         if (next_src) prefetch_pass<Real, MM>(!UP, Lp, next_src, lv, fd);
         if constexpr (TM) {
-            tmem::ld<NW>(tst.taddr + (uint32_t)(kfirst * WPR), tnw);
+            ts_fetch(kfirst, tnw);
             tmem::wait_ld<NW>(tnw);
             tmem::unpack<kU>(tnw, tR);
         } else {
@@ -723,21 +887,21 @@ __device__ __forceinline__ void dispatch_pass(const bool lw, const bool up, cons
                                               const Real wF, const Real wR, const Real bs, const Real bg,
                                               const void *src_lane, const void *next_src, PassFeed<Real, MM> &fd,
                                               const LevelView<Real> &lv, const TStore<Real> tst, double *bacc_up, double *bacc_dn,
-                                              const Real *coef) {
+                                              const Real *coef, const double tabT) {
     // coefficient rows of a band: [0] dn_last, [1] dn_gen, [2] up_first, [3] up_gen.  The value of layer k
     // of a downward pass belongs to interface k + 1: the plain accumulators are indexed by interface, the
     // partial-sum accumulators (kVarPartial) by layer.
     double *const dn = (V & kVarPartial) ? bacc_dn : bacc_dn + 1;
     if (lw) {
         if (up)
-            sweep_pass<Real, MM, true, true, FRESH, V>(lane, nl, Lp, wF, wR, bg, src_lane, next_src, fd, lv, tst, bacc_up, coef + 2 * Lp, coef + 3 * Lp);
+            sweep_pass<Real, MM, true, true, FRESH, V>(lane, nl, Lp, wF, wR, bg, src_lane, next_src, fd, lv, tst, bacc_up, coef + 2 * Lp, coef + 3 * Lp, tabT);
         else
-            sweep_pass<Real, MM, true, false, FRESH, V>(lane, nl, Lp, wF, wR, bs, src_lane, next_src, fd, lv, tst, dn, coef, coef + Lp);
+            sweep_pass<Real, MM, true, false, FRESH, V>(lane, nl, Lp, wF, wR, bs, src_lane, next_src, fd, lv, tst, dn, coef, coef + Lp, tabT);
     } else {
         if (up)
-            sweep_pass<Real, MM, false, true, FRESH, V>(lane, nl, Lp, wF, wR, bg, src_lane, next_src, fd, lv, tst, bacc_up, coef, coef);
+            sweep_pass<Real, MM, false, true, FRESH, V>(lane, nl, Lp, wF, wR, bg, src_lane, next_src, fd, lv, tst, bacc_up, coef, coef, tabT);
         else
-            sweep_pass<Real, MM, false, false, FRESH, V>(lane, nl, Lp, wF, wR, bs, src_lane, next_src, fd, lv, tst, dn, coef, coef);
+            sweep_pass<Real, MM, false, false, FRESH, V>(lane, nl, Lp, wF, wR, bs, src_lane, next_src, fd, lv, tst, dn, coef, coef, tabT);
     }
 }
 
@@ -745,7 +909,7 @@ __device__ __forceinline__ void dispatch_pass(const bool lw, const bool up, cons
 // live in registers); MM = 0 selects the resident-tau path.  Persistent CTAs: task = (column, c)
 // with c < ctas_per_col; warp w of the CTA sweeps part c * W + w of the column.
 template <typename Real, int MM, int V = 0>
-__global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
+__global__ void __launch_bounds__(variant_threads(V), 1) flux_kernel(const FluxArgs<Real> a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr bool FUSED = MM > 0;
     constexpr int MR = MM > 0 ? MM : 1;
@@ -754,7 +918,8 @@ __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
     const int tid = threadIdx.x, nthr = blockDim.x, W = nthr >> 5, warp = tid >> 5, lane = tid & 31;
     const int L = a.L, nl = a.L - 1, Lp = padded_layers(a.L), LS = Lp + kU, C = a.ctas_per_col;
 
-    const CtaSmem<Real, MM, V> lay(L);
+    const int ts_rows = (V & kVarMixed) ? Lp - a.tm_rows : -1;     // t-store layers in shared memory
+    const CtaSmem<Real, MM, V> lay(L, ts_rows);
     unsigned *lev_offdn = (unsigned *)(smem_raw + lay.off_offdn);
     unsigned *lev_offup = (unsigned *)(smem_raw + lay.off_offup);
     Real *lev_qg = (Real *)(smem_raw + lay.off_qg);
@@ -774,7 +939,8 @@ __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
     for (int i = lane; i < n_bacc; i += 32) bacc_up[i] = 0.0;
     // The t-store: the first replay of a run reads it with weight 0, so it has to hold finite numbers.
     __shared__ uint32_t s_tmem_base;
-    TStore<Real> tst{ts + lane, 0u};
+    TStore<Real> tst{ts + lane, 0u, a.tm_rows};
+    const double tabT = kExpTab[lane];             // this lane's entry of the 2^(j/32) table (kVarExpTable)
     if constexpr (TM) {
         if (warp == 0) tmem::acquire(&s_tmem_base, (uint32_t)a.tmem_cols);
         tmem::fence_before_sync();
@@ -784,8 +950,10 @@ __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
         uint32_t zero[NW];
 #pragma unroll
         for (int i = 0; i < NW; ++i) zero[i] = 0u;
-        for (int k0 = 0; k0 < Lp; k0 += kU) tmem::st<NW>(tst.taddr + (uint32_t)(k0 * WPR), zero);
+        for (int k0 = 0; k0 < a.tm_rows; k0 += kU) tmem::st<NW>(tst.taddr + (uint32_t)(k0 * WPR), zero);
         tmem::wait_st();
+        if constexpr ((V & kVarMixed) != 0)
+            for (int i = lane; i < ts_rows * 32; i += 32) ts[i] = Real(0);
     } else {
         for (int i = lane; i < Lp * 32; i += 32) ts[i] = Real(0);
     }
@@ -924,12 +1092,12 @@ __global__ void __launch_bounds__(256, 1) flux_kernel(const FluxArgs<Real> a) {
                 const void *src_lane = srcN;
                 if (s + 1 < s1) seg_params(s + 1, wN, srcN);
                 dispatch_pass<Real, MM, true, V>(lw, up, lane, nl, Lp, wF, wR, bs, bg, src_lane, s + 1 < e ? srcN : nullptr, fd, lv,
-                                                 tst, bacc_up, bacc_dn, coef);
+                                                 tst, bacc_up, bacc_dn, coef, tabT);
                 wR = wF;
                 up = !up;
             }
             dispatch_pass<Real, MM, false, V>(lw, up, lane, nl, Lp, Real(0), wR, bs, bg, nullptr, s < s1 ? srcN : nullptr, fd, lv,
-                                              tst, bacc_up, bacc_dn, coef);
+                                              tst, bacc_up, bacc_dn, coef, tabT);
             up = !up;
             // ---- partial band sums of this (warp, band) run -> scratch slot ---------------------------
             __syncwarp();

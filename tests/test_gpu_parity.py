@@ -234,6 +234,32 @@ def test_whole_column_mode_equals_split_mode():
         assert np.array_equal(many[k][:3], many[k][-3:])         # deterministic across CTAs
 
 
+@pytest.mark.parametrize('precision', ['f64', 'f32'])
+def test_tensor_memory_tstore_equals_shared_memory_tstore(precision, monkeypatch):
+    """The default kernel keeps the per-lane t-store in tensor memory (LDTM / STTM) and stages the
+    long-wave coefficient rows in shared memory; CMB200_FLUX_VARIANT=0 selects the plain kernel
+    (t-store in shared memory, coefficients broadcast with shuffles).  Same arithmetic in the same
+    order: the results are equal bit for bit, in both optical-depth sources, split and whole-column
+    mode."""
+    c = load_case('two_mol_nz41')
+    plan = make_plan(c, precision=precision, tables=True)
+    tau = oracle_tau(c)
+    for n_col in (3, 1300):
+        T, T_g, T_tau, albedo, q = batch_inputs(c, n_col, seed=11)
+        res = {}
+        for variant in ('0', None):
+            if variant is None:
+                monkeypatch.delenv('CMB200_FLUX_VARIANT', raising=False)
+            else:
+                monkeypatch.setenv('CMB200_FLUX_VARIANT', variant)
+            res[variant] = (plan.flux(T, T_g, T_tau=T_tau, q=q, albedo=albedo),
+                            plan.flux(T, T_g, tau=tau, albedo=albedo))
+        for a, b in zip(res['0'], res[None]):
+            for k in ('up', 'down', 'net', 'heating'):
+                assert np.isfinite(b[k]).all()
+                assert np.array_equal(a[k], b[k])
+
+
 def test_tau_id_selects_table():
     c = load_case('co2_nz50_earth')
     plan = make_plan(c)
