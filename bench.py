@@ -41,7 +41,7 @@ UNIT = 'column*level*bin/s'
 #   exp           : range reduction + degree-11 polynomial + scaling (CUDA exp)     EXP_FLOPS
 #   short-wave    : two running products, two source terms, two weighted sums       8
 #   long-wave     : additionally both emission recurrences                          + 14
-NCU_DRAM_BYTES_PER_COLUMN = (68.546560e6 + 51.996160e6) / 8880    # profiles/r01_flux_kernel_v6_ncu_full.txt
+NCU_DRAM_BYTES_PER_COLUMN = (68.149760e6 + 39.287040e6) / 8880    # profiles/r01_flux_kernel_v7_ncu_full.txt
 EXP_FLOPS = {'f64': 36, 'f32': 4}
 
 
@@ -322,6 +322,9 @@ def run_b200(a):
                 'unit': 'TFLOP/s', 'frac': achieved / peaks[key], 'traffic': None,
                 'kernel': 'flux_kernel<%s, fused>' % ('double' if a.precision == 'f64' else 'float'),
                 'kernel_ms': kernel_ms,
+                'kernel_variant': 't-store in tensor memory (LDTM/STTM), coefficient rows staged in shared memory, '
+                                  'segment-space table rows (csrc/flux_kernels.cuh; CMB200_FLUX_VARIANT=0 = plain kernel)',
+                'fp64_pipe_util_ncu': 0.532 if a.precision == 'f64' else None,   # profiles/r01_flux_kernel_v7_ncu_full.txt
                 **({'per_rank_kernel_ms': per_rank_kernel_ms} if world > 1 else {}),
                 'peak_source': 'cmb200_measure_peaks: independent-FMA issue-rate microbenchmark on this GPU '
                                '(MEASURED_PEAKS.json has no FP64/FP32 vector peak)',
@@ -334,7 +337,7 @@ def run_b200(a):
         pass
     roofline['hbm']['achieved_gbs'] = roofline['hbm']['algorithmic_bytes_per_step'] / (kernel_ms * 1e-3) / 1e9
     # DRAM traffic of the flux kernel from the committed `ncu --set full` capture (dram__bytes_read.sum +
-    # dram__bytes_write.sum = 120.5 MB for 8880 columns of this workload, profiles/r01_flux_kernel_v6_ncu_full.txt),
+    # dram__bytes_write.sum = 107.4 MB for 8880 columns of this workload, profiles/r01_flux_kernel_v7_ncu_full.txt),
     # scaled per column to this launch; only meaningful for the default FP64 workload shape.
     if a.precision == 'f64' and (L, M, w['nu'].size) == (100, 2, 10400):
         roofline['traffic'] = NCU_DRAM_BYTES_PER_COLUMN * n_col

@@ -153,10 +153,38 @@ static int flux_variant() {
     return e && *e ? atoi(e) : kDefaultVariant;
 }
 
+// The level table regathered into segment space (internal.cuh) for the fused path; CMB200_SEGMENT_TABLE=0
+// keeps the kernel on the bin-space table (A/B), and so does a failed allocation.
+template <typename Real>
+static bool ensure_segment_table(cmb200_plan *p, cudaStream_t s) {
+    const char *e = getenv("CMB200_SEGMENT_TABLE");
+    if ((e && *e == '0') || p->n_seg == 0) return false;
+    if (p->ks_valid) return true;
+    const int64_t spitch = (int64_t)p->n_seg * 32, rows = (int64_t)p->M * p->L * p->nT_pad;
+    const Real *KL;
+    Real *KS;
+    if constexpr (std::is_same<Real, double>::value) {
+        if (p->KS64.alloc((size_t)rows * spitch) != cudaSuccess) return cudaGetLastError(), false;
+        KL = p->KL64.p, KS = p->KS64.p;
+    } else {
+        if (p->KS32.alloc((size_t)rows * spitch) != cudaSuccess) return cudaGetLastError(), false;
+        KL = p->KL32.p, KS = p->KS32.p;
+    }
+    dim3 grid((unsigned)((spitch + 255) / 256), (unsigned)std::min<int64_t>(rows, 65535));
+    segment_table_kernel<Real><<<grid, 256, 0, s>>>(KL, rows, p->pitch, p->seg_bin.p, spitch, KS);
+    if (cudaGetLastError() != cudaSuccess) return false;
+    g_launches.fetch_add(1);
+    p->spitch = spitch;
+    p->ks_valid = true;
+    return true;
+}
+
 template <typename Real, int MM, int V>
 static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *Tint, cudaStream_t s) {
     const int L = p->L, Lp = padded_layers(L);
-    const double span = MM > 0 ? (double)MM * L * p->nT_pad * (double)p->pitch * sizeof(Real) / 16.0 : (double)L * (double)p->N;
+    const bool seg_space = MM > 0 && ensure_segment_table<Real>(p, s);
+    const int64_t pitch = seg_space ? p->spitch : p->pitch;
+    const double span = MM > 0 ? (double)MM * L * p->nT_pad * (double)pitch * sizeof(Real) / 16.0 : (double)L * (double)p->N;
     if (span >= 4294967296.0) {
         set_error("table / tau rows exceed the 32-bit row offsets of the flux kernel (%.3g units)", span);
         return CMB200_ERR_LIMIT;
@@ -216,7 +244,8 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     a.band_hi = p->band_hi;
     a.ctas_per_col = C;
     a.N = p->N;
-    a.pitch = p->pitch;
+    a.pitch = pitch;
+    a.seg_space = seg_space;
     a.n_col = io->n_col;
     a.n_tasks = n_tasks;
     a.geo = p->geo.p;
@@ -250,7 +279,10 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     a.albedo_scalar = io->albedo_scalar;
     a.tau = io->tau;
     a.tau_id = io->tau_id;
-    a.KL = std::is_same<Real, double>::value ? (const Real *)p->KL64.p : (const Real *)p->KL32.p;
+    if (seg_space)
+        a.KL = std::is_same<Real, double>::value ? (const Real *)p->KS64.p : (const Real *)p->KS32.p;
+    else
+        a.KL = std::is_same<Real, double>::value ? (const Real *)p->KL64.p : (const Real *)p->KL32.p;
     a.tidx = p->tidx.p;
     a.q = io->q;
     a.q_col_stride = io->q_per_column ? L : 0;
@@ -401,6 +433,7 @@ extern "C" int cmb200_plan_set_tables(cmb200_plan *plan, int32_t M, const cmb200
     plan->M = M;
     plan->nT_pad = nT_pad;
     plan->pitch = pitch;
+    plan->ks_valid = false;
     plan->partition.n_col = -1;
     return CMB200_OK;
 }

@@ -63,6 +63,7 @@ struct FluxArgs {
     unsigned long long *task_counter;   // zeroed before the launch
     long long *dbg;            // optional: sweep cycles per warp of CTA 0's first task (CMB200_DEBUG_TIMING)
     int tmem_cols, tmem_cpw;   // TMEM t-store: columns allocated per CTA, columns per warp (V & kVarTmem)
+    int seg_space;             // KL is the segment-space table (column = segment * 32 + lane), pitch its row length
     int tm_rows;               // layers of a warp's t-store kept in tensor memory (the rest in shared memory)
 };
 
@@ -1052,8 +1053,12 @@ __global__ void __launch_bounds__(variant_threads(V), 1) flux_kernel(const FluxA
         // first table rows of the pass, are fetched one pass ahead so that no pass starts on a miss.
         auto seg_params = [&](int sidx, Real &w, const void *&src) {
             w = __ldg(a.seg_w + (int64_t)sidx * 32 + lane);
-            const int64_t n = __ldg(a.seg_bin + (int64_t)sidx * 32 + lane);
-            src = FUSED ? (const void *)(a.KL + n) : (const void *)(tau_col + n);
+            if (FUSED && a.seg_space) {
+                src = (const void *)(a.KL + ((int64_t)sidx * 32 + lane));
+            } else {
+                const int64_t n = __ldg(a.seg_bin + (int64_t)sidx * 32 + lane);
+                src = FUSED ? (const void *)(a.KL + n) : (const void *)(tau_col + n);
+            }
         };
         PassFeed<Real, MM> fd;
         Real wN = Real(0);

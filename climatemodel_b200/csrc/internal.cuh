@@ -69,6 +69,13 @@ struct cmb200_plan {
     std::vector<int> nT;
     cmb::DevBuf<double> KL64, T_axes;  // T_axes[M][nT_pad]
     cmb::DevBuf<float> KL32;
+    // the same table in segment space for the flux kernel: KS[M][L][nT_pad][n_seg * 32], column
+    // s * 32 + lane = bin of lane `lane` of segment s, so that every row a warp loads is one aligned
+    // 256-byte (FP32: 128-byte) run; built on first use, dropped when segments or tables change
+    cmb::DevBuf<double> KS64;
+    cmb::DevBuf<float> KS32;
+    int64_t spitch = 0;
+    bool ks_valid = false;
     cmb::Partition partition;
     // per-call scratch kept between calls (grown on demand)
     cmb::DevBuf<double> Tint, scratch, coefbuf;

@@ -176,6 +176,7 @@ int build_segments(cmb200_plan *p) {
         CMB_CUDA(p->seg_w32.upload(w32.data(), w32.size()));
     CMB_CUDA(cudaDeviceSynchronize());
     p->partition.n_col = -1;
+    p->ks_valid = false;
     return CMB200_OK;
 }
 
