@@ -58,7 +58,8 @@ __device__ double enthalpy_of(const double *y, const double *p, double *terms, i
 __global__ void convective_adjust_kernel(int nl, int64_t n_col, const double *__restrict__ p_ref,
                                          const double *__restrict__ pw_ref, double small, double conv_thresh,
                                          double *__restrict__ T_dev, const uint8_t *__restrict__ active,
-                                         uint8_t *__restrict__ conv_level, int32_t *__restrict__ status) {
+                                         uint8_t *__restrict__ conv_level, int32_t *__restrict__ status,
+                                         const uint8_t *__restrict__ frozen) {
     extern __shared__ double smem[];
     const int warps = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t col = (int64_t)blockIdx.x * warps + warp;
@@ -72,7 +73,7 @@ __global__ void convective_adjust_kernel(int nl, int64_t n_col, const double *__
         pw[r] = pw_ref[r];
     }
     __syncthreads();
-    if (col >= n_col) return;
+    if (col >= n_col || (frozen && frozen[col])) return;
     double *Tcol = T_dev + col * nl;
     for (int r = lane; r < nl; r += 32) {
         T[r] = Tcol[nl - 1 - r];
@@ -197,14 +198,10 @@ __global__ void convective_adjust_kernel(int nl, int64_t n_col, const double *__
     if (status && lane == 0) status[col] = st;
 }
 
-}  // namespace cmb
-
-using namespace cmb;
-
-extern "C" int cmb200_convective_adjust(int32_t n_levels, int64_t n_col, const double *p_centre,
-                                        const double *p_power, double conv_thresh, double *T,
-                                        const uint8_t *active, uint8_t *convective_levels, int32_t *status,
-                                        void *stream) {
+// frozen[n_col] (device, may be NULL): columns to leave alone.
+int launch_convective_adjust(int32_t n_levels, int64_t n_col, const double *p_centre, const double *p_power,
+                             double conv_thresh, double *T, const uint8_t *active, uint8_t *convective_levels,
+                             int32_t *status, const uint8_t *frozen, void *stream) {
     CMB_CHECK_ARG(p_centre && p_power && T, "null pointer");
     CMB_CHECK_ARG(n_levels >= 3 && n_levels <= 256, "between 3 and 256 levels supported, got %d", n_levels);
     CMB_CHECK_ARG(n_col >= 0, "negative column count");
@@ -213,7 +210,19 @@ extern "C" int cmb200_convective_adjust(int32_t n_levels, int64_t n_col, const d
     const size_t smem = (size_t)(2 + 5 * warps) * n_levels * sizeof(double) + (size_t)warps * 2 * n_levels;
     CMB_CUDA(cudaFuncSetAttribute(convective_adjust_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     convective_adjust_kernel<<<(unsigned)((n_col + warps - 1) / warps), warps * 32, smem, (cudaStream_t)stream>>>(
-        n_levels, n_col, p_centre, p_power, 1e-10, conv_thresh, T, active, convective_levels, status);
+        n_levels, n_col, p_centre, p_power, 1e-10, conv_thresh, T, active, convective_levels, status, frozen);
     CMB_LAUNCHED();
     return CMB200_OK;
+}
+
+}  // namespace cmb
+
+using namespace cmb;
+
+extern "C" int cmb200_convective_adjust(int32_t n_levels, int64_t n_col, const double *p_centre,
+                                        const double *p_power, double conv_thresh, double *T,
+                                        const uint8_t *active, uint8_t *convective_levels, int32_t *status,
+                                        void *stream) {
+    return launch_convective_adjust(n_levels, n_col, p_centre, p_power, conv_thresh, T, active, convective_levels,
+                                    status, nullptr, stream);
 }

@@ -89,5 +89,8 @@ struct cmb200_plan {
 
 namespace cmb {
 int build_segments(cmb200_plan *p);
+int launch_convective_adjust(int32_t n_levels, int64_t n_col, const double *p_centre, const double *p_power,
+                             double conv_thresh, double *T, const uint8_t *active, uint8_t *convective_levels,
+                             int32_t *status, const uint8_t *frozen, void *stream);
 int spline_operator_host(const double *P, int L, std::vector<double> &At);
 }  // namespace cmb

@@ -23,6 +23,7 @@ struct cmb200_stepper {
     cmb::DevBuf<int32_t> conv_status;
     cmb::DevBuf<double> p_centre, p_power;     // reference order (surface first): p and (p / p_ref)^alpha
     double temp_change = 1.0, delta_temp_change = 0.01;
+    const uint8_t *frozen = nullptr;           // device, [n_col]: columns the updates leave alone (cmb200_stepper_set_frozen)
 };
 
 namespace cmb {
@@ -36,6 +37,7 @@ struct StepperArgs {
     double conv_mult;
     const uint8_t *conv_level;
     uint8_t *active;
+    const uint8_t *frozen;
     const double *net;
     double *T, *t, *dnf;
     double *delta_T, *max_tend, *dt, *prev_net;
@@ -49,7 +51,7 @@ __global__ void stepper_update_kernel(const StepperArgs a) {
     extern __shared__ double smem[];
     const int warps = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t col = (int64_t)blockIdx.x * warps + warp;
-    if (col >= a.n_col) return;
+    if (col >= a.n_col || (a.frozen && a.frozen[col])) return;
     const int L = a.L, nl = L - 1;
     double *diff = smem + (size_t)warp * 2 * L, *tend = diff + L;       // |net - prev| ; tendency per layer
     const double *net = a.net + col * L;
@@ -240,6 +242,7 @@ static int stepper_update(cmb200_stepper *s, const double *net, double *T, doubl
     a.conv_mult = conv_mult;
     a.conv_level = s->conv_level.p;
     a.active = s->active.p;
+    a.frozen = s->frozen;
     a.net = net;
     a.T = T;
     a.t = t;
@@ -290,8 +293,14 @@ extern "C" int cmb200_stepper_update_convective(cmb200_stepper *s, const double 
     int rc = stepper_update(s, net, T, t, delta_net_flux, net_flux_thresh, net_flux_percentile, changing_tau, 1,
                             conv_t_multiplier, stream);
     if (rc) return rc;
-    return cmb200_convective_adjust(s->plan->L - 1, s->n_col, s->p_centre.p, s->p_power.p, conv_thresh, T,
-                                    s->active.p, s->conv_level.p, s->conv_status.p, stream);
+    return cmb::launch_convective_adjust(s->plan->L - 1, s->n_col, s->p_centre.p, s->p_power.p, conv_thresh, T,
+                                         s->active.p, s->conv_level.p, s->conv_status.p, s->frozen, stream);
+}
+
+extern "C" int cmb200_stepper_set_frozen(cmb200_stepper *s, const uint8_t *frozen) {
+    CMB_CHECK_ARG(s, "null pointer");
+    s->frozen = frozen;
+    return CMB200_OK;
 }
 
 extern "C" int cmb200_stepper_state(const cmb200_stepper *s, double *delta_T, double *dt, int32_t *max_tend_ind,

@@ -69,6 +69,53 @@ class ColumnStepper:
             check(self._lib.cmb200_stepper_update(*head, C.c_void_p(stream)))
         return self.delta_net_flux
 
+    def evolve_to_equilibrium(self, flux_thresh=1e-3, convective_adjust=False, t_end=4.0, conv_thresh=1e-5,
+                              conv_t_multiplier=5, max_steps=1000000, check_every=16):
+        """``Atmosphere.evolve_to_equilibrium`` (base.py:266-335) for every column at once: all columns
+        step together, and a column stops -- is frozen on the device, its T, t and step state left as
+        they are -- as soon as ITS equilibrium test holds: max|net flux| or delta_net_flux below its
+        threshold (base.py:248-264; the threshold drops to 0.99 delta_net_flux of the column's second
+        step, base.py:315-316) or more than t_end years of model time.  The tests run on the device
+        with no host round trip; the host looks at the "all done" flag every check_every steps.
+        Returns the number of steps each column took (int64 tensor).  Raises ValueError when a
+        temperature goes negative (base.py:319-320) or max_steps is hit."""
+        import torch
+        dev = self.T.device
+        n = self.n_col
+        thr = torch.full((n,), float(flux_thresh), dtype=torch.float64, device=dev)
+        done = torch.zeros(n, dtype=torch.uint8, device=dev)
+        n_steps = torch.zeros(n, dtype=torch.int64, device=dev)
+
+        def years(t):                                   # t_years_days (base.py:23-27): years + days / 365
+            full_days = t / (24 * 60 ** 2)
+            whole = torch.floor(full_days / 365)
+            return whole + (full_days - 365 * whole) / 365
+        years0 = years(self.t)
+        check(self._lib.cmb200_stepper_set_frozen(self._h, C.c_void_p(done.data_ptr())))
+        try:
+            i = 0
+            while True:
+                running = done == 0
+                dnf = self.step(convective_adjust=convective_adjust, conv_thresh=conv_thresh,
+                                conv_t_multiplier=conv_t_multiplier)
+                n_steps += running
+                if i == 1:
+                    thr = torch.minimum(thr, 0.99 * dnf)
+                eq = (self.out['net'].abs().amax(dim=1) < thr) | (dnf < thr) | (years(self.t) - years0 > t_end)
+                done |= (eq & running).to(torch.uint8)
+                i += 1
+                if i % check_every == 0 or i >= max_steps:
+                    if float(self.T.min()) < 0:
+                        raise ValueError('Temperature is below zero')
+                    if bool(done.all()):
+                        break
+                    if i >= max_steps:
+                        raise ValueError('no equilibrium after %d steps' % max_steps)
+        finally:
+            torch.cuda.current_stream(dev).synchronize()
+            check(self._lib.cmb200_stepper_set_frozen(self._h, None))
+        return n_steps
+
     @property
     def net_flux(self):
         return self.out.get('net')

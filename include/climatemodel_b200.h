@@ -219,6 +219,11 @@ int cmb200_stepper_update_convective(cmb200_stepper *stepper, const double *net,
                                      double *delta_net_flux, double net_flux_thresh,
                                      double net_flux_percentile, int changing_tau, double conv_thresh,
                                      double conv_t_multiplier, void *stream);
+/* frozen[n_col] (DEVICE, read at every update; NULL clears): columns with a non-zero entry are
+ * skipped by cmb200_stepper_update / _update_convective -- T, t and the step state stay as they
+ * are.  This is how a batch follows Atmosphere.evolve_to_equilibrium (base.py:266-335), where a
+ * column stops stepping once it has reached equilibrium. */
+int cmb200_stepper_set_frozen(cmb200_stepper *stepper, const uint8_t *frozen);
 /* Copies of the per-column state to HOST arrays of n_col entries (any may be NULL);
  * max_tend_ind counts levels from the surface like the reference. */
 int cmb200_stepper_state(const cmb200_stepper *stepper, double *delta_T, double *dt,

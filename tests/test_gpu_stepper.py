@@ -163,3 +163,59 @@ def test_device_steps_with_convection_equal_host_steps():
             assert dnf_host == dnf[i], (step, i)
             moved += len(atm.time_step_info['convective_levels']) > 0
     assert moved >= 5                                           # every column convected at least once
+
+
+@pytest.mark.parametrize('convective', [False, True])
+def test_batched_evolve_to_equilibrium_equals_per_column_host_loop(convective):
+    """ColumnStepper.evolve_to_equilibrium against Atmosphere.evolve_to_equilibrium's loop
+    (base.py:266-335) run column by column on the host with the same net fluxes: every column stops
+    at its own step -- by the flux test, by the tightened threshold of the second step or by t_end --
+    and is frozen there while the others go on; final temperatures, times and step counts are EQUAL."""
+    import torch
+    from climatemodel_b200.plan import FluxPlan
+    from climatemodel_b200.radiation.base import t_years_days
+    from climatemodel_b200.radiation.columns import ColumnStepper
+    c = load_case('co2_nz50_earth')
+    order = np.argsort(c['P'])
+    P = c['P'][order]
+    L = P.size
+    plan = FluxPlan(P, c['nu'], c['bands'], tables=c['tables'])
+    rng = np.random.default_rng(21)
+    n_col = 6
+    T0 = c['T'][np.argsort(c['p'])] + rng.normal(0, 1.5, (n_col, L - 1)) * np.linspace(0.2, 3.0, n_col)[:, None]
+    if convective:
+        T0[:, -10:] += np.linspace(0, 10, 10)
+    T_g = c['T_g'] + rng.normal(0, 3, n_col)
+    q = np.ascontiguousarray(c['q'][:, order])
+    kw = dict(flux_thresh=0.5, t_end=0.02, convective_adjust=convective, conv_thresh=1e-9, conv_t_multiplier=3)
+    dev = torch.device('cuda', 0)
+    cols = ColumnStepper(plan, torch.tensor(T0, device=dev), torch.tensor(T_g, device=dev), q=torch.tensor(q, device=dev),
+                         albedo=0.3, temp_change=4.0)
+    n_steps = cols.evolve_to_equilibrium(check_every=5, max_steps=600, **kw).cpu().numpy()
+
+    # host: one Atmosphere per column; the net fluxes come from the same plan and the same batch shape
+    host = host_columns(P[::-1].copy(), T0)
+    for atm in host:
+        atm.time_step_info.update(DeltaT=4.0, MaxDeltaT=4.0)
+    T_host, t_host = T0.copy(), np.zeros(n_col)
+    thr, done, steps = np.full(n_col, kw['flux_thresh']), np.zeros(n_col, bool), np.zeros(n_col, int)
+    i = 0
+    while not done.all():
+        assert i < 600
+        net = plan.flux(T_host, T_g, q=q, albedo=0.3, outputs=('net',))['net']
+        for k, atm in enumerate(host):
+            if done[k]:
+                continue
+            t_host[k], dnf = atm.update_temp(t_host[k], net[k][::-1].reshape(-1, 1).copy(), convective_adjust=convective,
+                                             conv_thresh=kw['conv_thresh'], conv_t_multiplier=kw['conv_t_multiplier'])
+            T_host[k] = atm.T[::-1, 0]
+            steps[k] += 1
+            if i == 1:
+                thr[k] = min(thr[k], 0.99 * dnf)
+            years, days = t_years_days(t_host[k])
+            done[k] = atm.check_equilibrium(dnf, thr[k]) or years + days / 365 > kw['t_end']
+        i += 1
+    assert np.array_equal(n_steps, steps)
+    assert np.array_equal(cols.T.cpu().numpy(), T_host)
+    assert np.array_equal(cols.t.cpu().numpy(), t_host)
+    assert len(set(steps)) > 1 and steps.max() > 5            # the columns stopped at different steps
