@@ -163,6 +163,53 @@ def dtransmission_dq(p1, p2, p_all, nu_band, delta_nu_band, nu_all, tau, absorpt
     return out
 
 
+def emission_integrals(trans, P, p, beta_centre, beta_interface, beta_ground):
+    """The pressure integrals of ``RealGas.flux_integrals`` (real_gas.py:564-627) from a band's
+    transmission matrix, for all levels at once.
+
+    trans [L x L] = Trans_j(a, b) on the interfaces (only a <= b is read: the other triangle
+    overflows in the reference too); P [L] interfaces, p [L-1] cell centres, ascending;
+    beta_centre [L-1], beta_interface [L], beta_ground = pi B(band centre, .) at the cell centres,
+    at the interfaces and at T_g.  With D_up[i, k] = (Trans(i, k+1) - Trans(i, k)) / (P_k+1 - P_k)
+    the upward integral from interface i runs over [P_i, p_i .. p_L-2, P_L-1] with the integrand
+    beta_interface[i] D_up[i, i] at its first point, beta_centre[k] D_up[i, k] at the centres and
+    beta_ground D_up[i, L-2] at the surface; the downward one to interface m over
+    [P_0, p_0 .. p_m-1, P_m] with D_dn[k, m] = (Trans(k+1, m) - Trans(k, m)) / (P_k+1 - P_k),
+    beta_interface[0] at the top and beta_interface[m] at the end.  Trapezoid rule, as np.trapz.
+    Returns (integral_up [L], integral_down [L]); integral_up[L-1] = integral_down[0] = 0."""
+    trans = np.asarray(trans, dtype=float)
+    P = np.asarray(P, dtype=float).reshape(-1)
+    p = np.asarray(p, dtype=float).reshape(-1)
+    bc = np.asarray(beta_centre, dtype=float).reshape(-1)
+    bi = np.asarray(beta_interface, dtype=float).reshape(-1)
+    bg = float(np.ravel(beta_ground)[0])
+    L = P.size
+    if trans.shape != (L, L) or p.size != L - 1 or bc.size != L - 1 or bi.size != L:
+        raise ValueError('emission_integrals: inconsistent shapes')
+    dP, dpc = np.diff(P), np.diff(p)
+    ones = np.ones((L, L), dtype=bool)
+    with np.errstate(all='ignore'):
+        D_up = np.where(np.triu(ones[:, :L - 1]), np.diff(trans, axis=1) / dP[None, :], 0.0)       # [i, k], k >= i
+        D_dn = np.where(np.triu(ones[:L - 1, :], 1), np.diff(trans, axis=0) / dP[:, None], 0.0)    # [k, m], k < m
+    rows = np.arange(L - 1)
+    # upward
+    G = D_up * bc[None, :]
+    first = 0.5 * (bi[:-1] * D_up[rows, rows] + G[rows, rows]) * (p - P[:-1])
+    inner = np.where(np.triu(ones[:, :L - 2]), 0.5 * (G[:, :-1] + G[:, 1:]) * dpc[None, :], 0.0).sum(axis=1)
+    last = 0.5 * (G[:, -1] + bg * D_up[:, -1]) * (P[-1] - p[-1])
+    up = np.zeros(L)
+    up[:-1] = -(first + inner[:-1] + last[:-1])
+    # downward
+    G = D_dn * bc[:, None]
+    first = 0.5 * (bi[0] * D_dn[0, :] + G[0, :]) * (p[0] - P[0])
+    inner = np.where(np.triu(ones[:L - 2, :], 2), 0.5 * (G[:-1, :] + G[1:, :]) * dpc[:, None], 0.0).sum(axis=0)
+    cols = np.arange(1, L)
+    last = 0.5 * (G[cols - 1, cols] + bi[1:] * D_dn[cols - 1, cols]) * (P[1:] - p)
+    down = np.zeros(L)
+    down[1:] = first[1:] + inner[1:] + last
+    return up, down
+
+
 def __getattr__(name):
     # RealGas is defined in real_gas_model (which imports this module); resolve lazily so that
     # ``from climatemodel_b200.radiation.real_gas import RealGas`` works like the reference import.

@@ -17,7 +17,7 @@ from ..constants import T_sun, R_sun, AU, p_surface_earth, p_toa_earth, sigma
 from ..plan import FluxPlan, bands_from_nu_bands
 from . import grids
 from .base import Atmosphere
-from .real_gas import get_absorption_coef, optical_depth
+from .real_gas import B_wavenumber, emission_integrals, get_absorption_coef, optical_depth, transmission
 from .real_gas_data import hitran as _hitran
 from .real_gas_data.specific_humidity import molecules, ppmv_from_humidity
 
@@ -176,6 +176,22 @@ class RealGas(Atmosphere):
         surface = surf['up'][0][0].copy()
         atmos = np.where(self.nu_bands['sw'], 0.0, up[0] - surface)
         return up, down, {'surface': surface, 'atmos': atmos}
+
+    def flux_integrals(self, j, T_interface):
+        """(integral_up, integral_down), each [nz]: the emission integrals of long-wave band j
+        (real_gas.py:564-627) for interface temperatures T_interface [nz] (or [nz x 1], as get_flux
+        passes them).  The band's transmission matrix comes from the GPU (``transmission``), the
+        Planck terms from ``B_wavenumber``; the pressure integrals are ``emission_integrals``."""
+        P = np.asarray(self.p_interface, dtype=float)[:, 0]
+        centre = self.nu_bands['centre'][j]
+        trans = transmission(P, P, P, self.nu_bands['range'][j], self.nu_bands['delta'][j], self.nu, self.tau_interface)
+        T_int = np.asarray(T_interface, dtype=float).reshape(-1)
+        beta = lambda T: np.pi * B_wavenumber(centre, np.asarray(T, dtype=float).reshape(-1))
+        return emission_integrals(trans, P, np.asarray(self.p, dtype=float)[:, 0], beta(self.T), beta(T_int),
+                                  beta([float(np.ravel(self.T_g)[0])])[0])
+
+    def __str__(self):
+        return 'Real Gas'
 
     def _refresh_flux(self):
         out = self._evaluate(('up', 'down', 'net'))

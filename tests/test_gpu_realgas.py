@@ -112,3 +112,24 @@ def test_auto_Tg_guess_balances_the_column(mods):
     # and optical depth are rebuilt for the new T_g, so the sum is no longer exactly zero)
     assert abs(float(np.ravel(gas.T_g)[0]) - 259.8448678790483) < 1e-8
     assert abs(np.sum(gas.net_flux) - (-7.506481761631903)) < 1e-8
+
+
+@pytest.mark.parametrize('name', ['co2_nz50_earth', 'two_mol_nz41'])
+def test_flux_integrals_method(mods, name):
+    """``RealGas.flux_integrals(j, T_interface)`` (real_gas.py:564-627) against the unmodified
+    reference's method (tests/golden/flux_integrals.npz): two long-wave bands, the spline interface
+    temperatures and a perturbed set, passed as [nz] and as [nz x 1]."""
+    import os
+    from util import GOLDEN
+    g = np.load(os.path.join(GOLDEN, 'flux_integrals.npz'))
+    gas = build(mods, name)
+    assert str(gas) == 'Real Gas'
+    for tag in ('a', 'b'):
+        key = '%s_%s_' % (name, tag)
+        j = int(g[key + 'band'])
+        for ttag in ('spline', 'pert'):
+            T_int = g[key + ttag + '_T_interface']
+            up, dn = gas.flux_integrals(j, T_int if ttag == 'pert' else T_int.reshape(-1, 1))
+            assert up.shape == (gas.nz,) and dn.shape == (gas.nz,)
+            assert relmax(up, g[key + ttag + '_up']) < 1e-10
+            assert relmax(dn, g[key + ttag + '_down']) < 1e-10

@@ -97,3 +97,31 @@ def test_bands_from_nu_bands_rejects_non_contiguous():
     nu = np.arange(0., 100., 10.)
     with pytest.raises(ValueError):
         bands_from_nu_bands(nu, {'range': [np.array([0., 20.])], 'centre': [0.], 'delta': [20.], 'sw': [False]})
+
+
+def test_emission_integrals_against_reference_vectors():
+    """``real_gas.emission_integrals`` (the host half of ``RealGas.flux_integrals``, real_gas.py:564-627)
+    against tests/golden/flux_integrals.npz, produced by the unmodified reference's method for two
+    long-wave bands of two configurations, with the spline interface temperatures and a perturbed set."""
+    import os
+    import oracle.realgas_oracle as orc
+    from util import GOLDEN
+    from climatemodel_b200.radiation.real_gas import emission_integrals
+    g = np.load(os.path.join(GOLDEN, 'flux_integrals.npz'))
+    n = 0
+    for name in ('co2_nz50_earth', 'two_mol_nz41'):
+        P, p, T, T_g, centre = (g[name + '_' + k] for k in ('P', 'p', 'T', 'T_g', 'centre'))
+        for tag in ('a', 'b'):
+            key = '%s_%s_' % (name, tag)
+            c = centre[int(g[key + 'band'])]
+            beta = lambda x: np.pi * orc.planck_wavenumber(c, np.asarray(x, dtype=float))
+            trans = g[key + 'trans_upper'].copy()
+            trans[np.tril_indices(P.size, -1)] = np.inf          # the reference's lower triangle overflows: must not be read
+            for ttag in ('spline', 'pert'):
+                up, dn = emission_integrals(trans, P, p, beta(T), beta(g[key + ttag + '_T_interface']), beta(T_g))
+                for got, want in ((up, g[key + ttag + '_up']), (dn, g[key + ttag + '_down'])):
+                    assert np.isfinite(got).all()
+                    assert np.abs(got - want).max() <= 1e-12 * np.abs(want).max()
+                assert up[-1] == 0 and dn[0] == 0
+                n += 1
+    assert n == 8
