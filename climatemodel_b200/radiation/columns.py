@@ -157,3 +157,31 @@ def convective_adjustment_device(p, T, conv_thresh=1e-5):
     if surface_first:
         T.copy_(work.flip(1))
     return T, status
+
+
+# ---- independent columns over several ranks (column sharding, no data-path collective) ------
+def column_share(n_all, rank, world):
+    """Global indices of the columns rank `rank` of `world` steps: round-robin, so that neighbours
+    (in latitude, say), which cost about the same, land on different ranks."""
+    return np.arange(rank, n_all, world)
+
+
+def gather_columns(rows, n_all, rank, world, group=None):
+    """rows: torch tensor [len(column_share(n_all, rank, world)), k] of per-column results on this
+    rank (any device torch.distributed's backend handles).  Returns the complete [n_all, k] table in
+    global column order on every rank: one all-gather of equally padded blocks -- the only
+    communication of a column-sharded run, after the stepping is done."""
+    import torch
+    import torch.distributed as dist
+    if world == 1:
+        return rows
+    pad = -(-n_all // world)
+    block = torch.zeros((pad, rows.shape[1]), dtype=rows.dtype, device=rows.device)
+    block[:rows.shape[0]] = rows
+    blocks = [torch.zeros_like(block) for _ in range(world)]
+    dist.all_gather(blocks, block, group=group)
+    full = torch.zeros((n_all, rows.shape[1]), dtype=rows.dtype, device=rows.device)
+    for r in range(world):
+        idx = torch.as_tensor(column_share(n_all, r, world), device=rows.device)
+        full[idx] = blocks[r][:idx.numel()]
+    return full

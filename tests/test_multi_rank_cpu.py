@@ -107,3 +107,31 @@ def test_wavenumber_shard_count_rule():
     assert [wavenumber_shards(332, n) for n in (1, 2, 4, 8)] == [1, 2, 2, 2]        # bench workload, 10.4k bins
     assert [wavenumber_shards(31250, n) for n in (2, 4, 8)] == [2, 4, 8]            # 1M-bin sweep
     assert wavenumber_shards(100, 8) == 1 and wavenumber_shards(400, 6) == 3
+
+
+# ---- column sharding (independent columns, BASELINE configs[4]): split and gather ------------------------
+def _column_worker(rank, world, port, n_all, out_dir):
+    os.environ.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port))
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        from climatemodel_b200.radiation.columns import column_share, gather_columns
+        mine = column_share(n_all, rank, world)
+        rows = torch.tensor(np.stack([mine * 10.0 + k for k in range(3)], axis=1))      # stand-in for (T, t, steps)
+        full = gather_columns(rows, n_all, rank, world)
+        np.save(os.path.join(out_dir, 'full_%d.npy' % rank), full.numpy())
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize('n_all', [7, 8])
+def test_column_shares_tile_the_ensemble_and_gather_restores_order(tmp_path, n_all):
+    from climatemodel_b200.radiation.columns import column_share
+    for world in (1, 2, 3, 8):
+        shares = [column_share(n_all, r, world) for r in range(world)]
+        assert np.array_equal(np.sort(np.concatenate(shares)), np.arange(n_all))
+        assert max(map(len, shares)) - min(map(len, shares)) <= 1
+    world = 2
+    mp.spawn(_column_worker, args=(world, _free_port(), n_all, str(tmp_path)), nprocs=world, join=True)
+    want = np.stack([np.arange(n_all) * 10.0 + k for k in range(3)], axis=1)
+    for r in range(world):
+        assert np.array_equal(np.load(tmp_path / ('full_%d.npy' % r)), want)

@@ -40,7 +40,7 @@ def main():
     import torch.distributed as dist
     from climatemodel_b200 import _lib, synthetic
     from climatemodel_b200.plan import FluxPlan
-    from climatemodel_b200.radiation.columns import ColumnStepper
+    from climatemodel_b200.radiation.columns import ColumnStepper, column_share, gather_columns
 
     world = int(os.environ.get('WORLD_SIZE', '1'))
     rank = int(os.environ.get('RANK', '0'))
@@ -58,7 +58,7 @@ def main():
     lat_all = np.repeat(lat, 2)
     ppmv_all = np.tile([370.0, 740.0], a.latitudes)
     n_all = lat_all.size
-    mine = np.arange(rank, n_all, world)                   # round-robin: neighbours in latitude cost the same
+    mine = column_share(n_all, rank, world)               # round-robin: neighbours in latitude cost the same
     T_g = 300.0 - 50.0 * np.sin(np.radians(lat_all[mine])) ** 2
     n_col = mine.size
     T0 = np.repeat(T_g[:, None], L - 1, axis=1)            # isothermal start (real_gas.py:285-289)
@@ -84,22 +84,13 @@ def main():
     out = torch.cat((cols.T, cols.t[:, None], n_steps.to(torch.float64)[:, None],
                      cols.net_flux.abs().amax(dim=1, keepdim=True)), dim=1)          # [n_col, L-1 + 3]
     stats = torch.tensor([wall, float(n_steps.sum()), float(n_steps.max()), float(launches)], dtype=torch.float64, device=dev)
+    full = gather_columns(out, n_all, rank, world).cpu().numpy()
     if world > 1:
-        pad = -(-n_all // world)
-        buf = torch.zeros((pad, out.shape[1]), dtype=torch.float64, device=dev)
-        buf[:n_col] = out
-        gathered = [torch.zeros_like(buf) for _ in range(world)]
-        dist.all_gather(gathered, buf)
         all_stats = [torch.zeros_like(stats) for _ in range(world)]
         dist.all_gather(all_stats, stats)
-        full = np.zeros((n_all, out.shape[1]))
-        for r in range(world):
-            idx = np.arange(r, n_all, world)
-            full[idx] = gathered[r][:idx.size].cpu().numpy()
         st = torch.stack(all_stats).cpu().numpy()
         wall, col_steps, max_steps, launches = st[:, 0].max(), st[:, 1].sum(), st[:, 2].max(), st[:, 3].sum()
     else:
-        full = out.cpu().numpy()
         wall, col_steps, max_steps, launches = stats.cpu().numpy()
     if rank == 0:
         T_fin = full[:, :L - 1]
