@@ -80,6 +80,7 @@ SIGNATURES = {
                                                    C.c_double, C.c_double, C.c_int, C.c_double, C.c_double,
                                                    C.c_void_p]),
     'cmb200_stepper_set_frozen': (C.c_int, [C.c_void_p, C.c_void_p]),
+    'cmb200_stepper_set_level_order': (C.c_int, [C.c_void_p, C.c_int]),
     'cmb200_stepper_state': (C.c_int, [C.c_void_p, c_double_p, c_double_p, c_int32_p, c_int32_p]),
     'cmb200_grey_flux_host': (C.c_int, [C.c_int32, C.c_int64, C.c_double] + [c_double_p] * 11),
     'cmb200_plan_create': (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.POINTER(Constants), C.c_int32,

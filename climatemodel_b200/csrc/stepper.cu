@@ -4,13 +4,20 @@
 // time_step_info (base.py:137-141); here it is a structure of arrays, one entry per column, and
 // one warp advances one column:
 //   tendency = g/c_p d(net)/dp per layer                                         (base.py:166-168)
-//   updated layers = |net flux at the layer's lower interface| > threshold, minus frozen layers
+//   updated layers = |net flux at the layer's first interface in the caller's level order| >
+//   threshold, minus frozen layers                                               (base.py:171-172)
 //   delta_net_flux = percentile of |net - previous net| (NumPy's linear method)  (base.py:173)
 //   dt = DeltaT / |largest tendency among updated layers|, DeltaT adapted to oscillation /
 //   stagnation of the layer that sets it, persistent offenders frozen            (base.py:197-246)
 //   T += dt * tendency on the updated layers,  t += dt
-// Levels are stored like everywhere in this library (index 0 = top of atmosphere); the
-// reference's indices (0 = surface) decide ties of the arg-max and are what max_tend_ind holds.
+// Levels are stored like everywhere in this library (index 0 = top of atmosphere).  The reference
+// works on the arrays in the caller's order: RealGas keeps p_interface ascending (index 0 = top,
+// real_gas.py:281), the grey model descending (index 0 = surface).  That order decides which
+// interface gates layer i (net[i], the layer's first interface), the first-index tie-break of the
+// arg-max and the numbering of MaxTendInd / RemoveInd; `top_first` selects it
+// (cmb200_stepper_set_level_order; default 1 = RealGas).  The per-layer byte arrays (removed,
+// active, conv_level) are always stored surface first, which is what the convective adjustment
+// kernel reads.
 #include "internal.cuh"
 
 struct cmb200_stepper {
@@ -23,6 +30,7 @@ struct cmb200_stepper {
     cmb::DevBuf<int32_t> conv_status;
     cmb::DevBuf<double> p_centre, p_power;     // reference order (surface first): p and (p / p_ref)^alpha
     double temp_change = 1.0, delta_temp_change = 0.01;
+    int top_first = 1;                         // reference level numbering: 1 = RealGas (index 0 = top), 0 = surface first
     const uint8_t *frozen = nullptr;           // device, [n_col]: columns the updates leave alone (cmb200_stepper_set_frozen)
 };
 
@@ -33,7 +41,7 @@ struct StepperArgs {
     int64_t n_col;
     const double *Pint;
     double g_over_cp, thresh, quantile, max_delta_T, delta_T_step;
-    int changing_tau, convective;
+    int changing_tau, convective, top_first;
     double conv_mult;
     const uint8_t *conv_level;
     uint8_t *active;
@@ -86,11 +94,13 @@ __global__ void stepper_update_kernel(const StepperArgs a) {
     }
 
     // ---- layers to update and the one with the largest |tendency| (first in the reference's order) ----
+    const int tf = a.top_first;
     double best = -1.0;
     int best_r = -1, n_active = 0;
     for (int k = lane; k < nl; k += 32) {
-        const int r = nl - 1 - k;                                       // reference level index
-        const bool act = normal ? (fabs(net[k + 1]) > a.thresh && !removed[r]) : true;
+        const int rs = nl - 1 - k;                                      // storage index of the byte arrays
+        const int r = tf ? k : rs;                                      // reference level index
+        const bool act = normal ? (fabs(net[tf ? k : k + 1]) > a.thresh && !removed[rs]) : true;
         if (act) {
             ++n_active;
             const double m = fabs(tend[k]);
@@ -116,7 +126,8 @@ __global__ void stepper_update_kernel(const StepperArgs a) {
     if (n_active > 0 && lane == 0) {
         double DeltaT = a.delta_T[col];
         int n1 = a.n_same[col], n2 = a.n_same2[col], n_rem = a.n_removed[col];
-        const double tnd = tend[nl - 1 - best_r];
+        const int best_k = tf ? best_r : nl - 1 - best_r, best_rs = nl - 1 - best_k;
+        const double tnd = tend[best_k];
         const bool same_level = best_r == a.max_tend_ind[col];
         const bool same_sign = sign_of(tnd) == sign_of(a.max_tend[col]);
         if (same_level && !same_sign) {
@@ -132,14 +143,14 @@ __global__ void stepper_update_kernel(const StepperArgs a) {
             n2 = 0;
         }
         if ((n1 > 1 && n2 > 10) || (n1 > 20 && n2 == 0) || (n_rem > 3 && n1 + n2 > 0)) {
-            removed[best_r] = 1;
+            removed[best_rs] = 1;
             n_rem += 1;
             n1 = 0;
             n2 = 0;
         }
         dt = DeltaT / fabs(tnd);
         if (isinf(dt)) dt = 24.0 * 60.0 * 60.0;
-        if (a.convective && a.conv_level[col * nl + best_r]) dt = dt * a.conv_mult;     // base.py:181-184
+        if (a.convective && a.conv_level[col * nl + best_rs]) dt = dt * a.conv_mult;    // base.py:181-184
         a.delta_T[col] = DeltaT;
         a.n_same[col] = n1;
         a.n_same2[col] = n2;
@@ -153,12 +164,13 @@ __global__ void stepper_update_kernel(const StepperArgs a) {
 
     // ---- T += dt * tendency on the layers chosen above (a layer frozen in this very step still moves) --
     double *T = a.T + col * nl;
+    const int best_k_all = best_r < 0 ? -1 : (tf ? best_r : nl - 1 - best_r);
     for (int k = lane; k < nl; k += 32) {
-        const int r = nl - 1 - k;
-        const bool was_removed_before = removed[r] && r != best_r;
-        const bool act = normal ? (fabs(net[k + 1]) > a.thresh && !was_removed_before) : true;
+        const int rs = nl - 1 - k;
+        const bool was_removed_before = removed[rs] && k != best_k_all;
+        const bool act = normal ? (fabs(net[tf ? k : k + 1]) > a.thresh && !was_removed_before) : true;
         if (act) T[k] = __dadd_rn(T[k], __dmul_rn(dt, tend[k]));
-        if (a.active) a.active[col * nl + r] = act;
+        if (a.active) a.active[col * nl + rs] = act;
     }
     for (int i = lane; i < L; i += 32) prev[i] = net[i];
     if (lane == 0) {
@@ -239,6 +251,7 @@ static int stepper_update(cmb200_stepper *s, const double *net, double *T, doubl
     a.delta_T_step = s->delta_temp_change;
     a.changing_tau = changing_tau;
     a.convective = convective;
+    a.top_first = s->top_first;
     a.conv_mult = conv_mult;
     a.conv_level = s->conv_level.p;
     a.active = s->active.p;
@@ -295,6 +308,12 @@ extern "C" int cmb200_stepper_update_convective(cmb200_stepper *s, const double 
     if (rc) return rc;
     return cmb::launch_convective_adjust(s->plan->L - 1, s->n_col, s->p_centre.p, s->p_power.p, conv_thresh, T,
                                          s->active.p, s->conv_level.p, s->conv_status.p, s->frozen, stream);
+}
+
+extern "C" int cmb200_stepper_set_level_order(cmb200_stepper *s, int top_first) {
+    CMB_CHECK_ARG(s, "null pointer");
+    s->top_first = top_first ? 1 : 0;
+    return CMB200_OK;
 }
 
 extern "C" int cmb200_stepper_set_frozen(cmb200_stepper *s, const uint8_t *frozen) {

@@ -19,10 +19,17 @@ from .._lib import check
 
 class ColumnStepper:
     def __init__(self, plan, T, T_g, q=None, T_tau=None, tau=None, tau_id=None, albedo=0.3, temp_change=1,
-                 delta_temp_change=0.01):
+                 delta_temp_change=0.01, level_order='top_first'):
         """plan: FluxPlan; T [n_col, L-1], T_g [n_col] and the optical-depth source (q, T_tau or
         tau, tau_id) as for ``FluxPlan.flux_device`` (torch float64 CUDA tensors).  T is advanced in
-        place.  Level index 0 is the top of the atmosphere, as in ``FluxPlan``."""
+        place.  Level index 0 is the top of the atmosphere, as in ``FluxPlan``.
+
+        level_order: the level numbering of the model each column stands for -- it decides which
+        interface's |net flux| gates a layer (base.py:171), arg-max ties (base.py:209) and the
+        numbering of MaxTendInd.  'top_first' (default) = ``RealGas`` (p_interface ascending,
+        real_gas.py:281); 'surface_first' = an ``Atmosphere`` whose arrays start at the surface."""
+        if level_order not in ('top_first', 'surface_first'):
+            raise ValueError("level_order must be 'top_first' or 'surface_first'")
         import torch
         self.plan, self.T, self.T_g = plan, T, T_g
         self.source = dict(q=q, T_tau=T_tau, tau=tau, tau_id=tau_id, albedo=albedo)
@@ -34,6 +41,8 @@ class ColumnStepper:
         self._h = C.c_void_p()
         check(self._lib.cmb200_stepper_create(C.byref(self._h), plan._h, self.n_col, float(temp_change),
                                               float(delta_temp_change)))
+        self.level_order = level_order
+        check(self._lib.cmb200_stepper_set_level_order(self._h, int(level_order == 'top_first')))
         # cell centres in the reference's order (surface first) and (p / p_ref)^alpha as NumPy evaluates it
         from .convective_adjustment import g, c_p_dry, p_surface_earth, R_specific
         P_ref = np.asarray(plan.P, dtype=float)[::-1]
@@ -121,8 +130,8 @@ class ColumnStepper:
         return self.out.get('net')
 
     def state(self):
-        """Host copies of the per-column time-step state: DeltaT, dt, MaxTendInd (levels counted from
-        the surface like the reference), number of frozen levels."""
+        """Host copies of the per-column time-step state: DeltaT, dt, MaxTendInd (numbered in
+        ``level_order``), number of frozen levels."""
         n = self.n_col
         dT, dt = np.zeros(n), np.zeros(n)
         ind, rem = np.zeros(n, dtype=np.int32), np.zeros(n, dtype=np.int32)

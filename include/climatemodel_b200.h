@@ -189,6 +189,13 @@ int cmb200_stepper_create(cmb200_stepper **stepper, cmb200_plan *plan, int64_t n
                           double temp_change, double delta_temp_change);
 int cmb200_stepper_reset(cmb200_stepper *stepper);
 int cmb200_stepper_destroy(cmb200_stepper *stepper);
+/* Level numbering of the caller the stepper stands in for.  The reference works on its arrays in
+ * the order the model stores them: RealGas ascending in pressure (index 0 = top of atmosphere,
+ * real_gas.py:281), the grey model surface first (grey.py:207-249).  update_temp gates layer i on
+ * |net_flux[i]| (base.py:171), np.argmax breaks ties by first index (base.py:209) and MaxTendInd /
+ * RemoveInd hold indices in that order.  top_first = 1 (default): RealGas numbering;
+ * top_first = 0: surface-first numbering.  The device arrays stay top first either way. */
+int cmb200_stepper_set_level_order(cmb200_stepper *stepper, int top_first);
 /* Atmosphere.update_temp with convective_adjust=False (base.py:166-196) and update_time_step
  * (base.py:197-246) for every column at once.  DEVICE pointers: net[n_col][L] from cmb200_flux,
  * T[n_col][L-1] updated in place, t[n_col] (seconds) advanced by each column's own dt,
@@ -225,7 +232,7 @@ int cmb200_stepper_update_convective(cmb200_stepper *stepper, const double *net,
  * column stops stepping once it has reached equilibrium. */
 int cmb200_stepper_set_frozen(cmb200_stepper *stepper, const uint8_t *frozen);
 /* Copies of the per-column state to HOST arrays of n_col entries (any may be NULL);
- * max_tend_ind counts levels from the surface like the reference. */
+ * max_tend_ind is numbered in the order chosen by cmb200_stepper_set_level_order. */
 int cmb200_stepper_state(const cmb200_stepper *stepper, double *delta_T, double *dt,
                          int32_t *max_tend_ind, int32_t *n_removed);
 

@@ -3,10 +3,17 @@ UNMODIFIED reference.  Build container only (needs /root/reference):
 
     python tests/golden/make_golden_integrals.py
 
-For two of the configurations of make_golden.py it calls the reference method for two long-wave
+For two of the configurations of make_golden.py it calls the reference method for three long-wave
 bands with the spline interface temperatures and with a perturbed set, and stores the inputs the
 method reads (band transmission matrix -- upper triangle, the lower one overflows --, grids,
 temperatures) next to its outputs in ``flux_integrals.npz``.
+
+Band choice: the integrals are sums of beta * (Trans(i,k+1) - Trans(i,k)), so a band whose
+whole-column transmission is 1 - 1e-11 yields integrals that are rounding noise of the
+reference's own evaluation (and a band with Trans == 1 yields exact zeros).  Tags 'a' and 'b'
+are therefore the two long-wave bands with the largest absorption 1 - Trans(0, L-1) (well
+conditioned: the 1e-10 gate applies); tag 'c' is the most transparent band that still absorbs
+(1 - Trans > 0), kept to exercise the conditioning-aware bound of the test.
 """
 import os
 import sys
@@ -46,10 +53,15 @@ def main():
         Ti = InterpolatedUnivariateSpline(gas.p, gas.T)(gas.p_interface).reshape(-1)
         Ti[-1] = gas.T_g
         Ti_pert = Ti + rng.normal(0, 2.0, Ti.size)
-        for tag, j in (('a', int(lw[1])), ('b', int(lw[-1]))):
+        absorb = np.array([1.0 - rg.transmission(P[:1], P[-1:], P, gas.nu_bands['range'][j], gas.nu_bands['delta'][j],
+                                                 gas.nu, gas.tau_interface)[0, 0] for j in lw])
+        order = np.argsort(-absorb)
+        weakest = [k for k in order if absorb[k] > 0][-1]
+        for tag, j in (('a', int(lw[order[0]])), ('b', int(lw[order[1]])), ('c', int(lw[weakest]))):
             Tr = rg.transmission(P, P, P, gas.nu_bands['range'][j], gas.nu_bands['delta'][j], gas.nu, gas.tau_interface)
             key = '%s_%s_' % (name, tag)
             out[key + 'band'] = j
+            out[key + 'absorption'] = 1.0 - Tr[0, -1]
             out[key + 'trans_upper'] = np.triu(np.nan_to_num(Tr, nan=0.0, posinf=0.0))
             for ttag, T_int in (('spline', Ti), ('pert', Ti_pert)):
                 with np.errstate(all='ignore'):

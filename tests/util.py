@@ -30,4 +30,8 @@ def relmax(a, b):
     """Norm-wise relative error max|a-b| / max|b| (the parity metric of SURVEY.md 7.3-3)."""
     a = np.asarray(a, dtype=float)
     b = np.asarray(b, dtype=float)
-    return float(np.abs(a - b).max() / np.abs(b).max())
+    scale = float(np.abs(b).max())
+    diff = float(np.abs(a - b).max())
+    if scale == 0.0:            # all-zero reference: exact agreement is 0, anything else is infinite
+        return 0.0 if diff == 0.0 else float('inf')
+    return diff / scale
