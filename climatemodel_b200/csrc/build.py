@@ -42,6 +42,8 @@ def build(force=False, verbose=False):
     experiments = [v for v in os.environ.get('CMB200_EXPERIMENTS', '').split(',') if v.strip()]
     if experiments:      # extra flux kernel variants for tools/ab_flux_variants.py (flux.cu)
         extra.append('-DCMB_FLUX_EXPERIMENTS(X)=' + ' '.join('X(%d)' % int(v) for v in experiments))
+    if os.environ.get('CMB200_DEV'):      # kernel development: bench shapes only (flux.cu)
+        extra.append('-DCMB_DEV_BUILD')
     cmd = [nvcc_path()] + NVCC_FLAGS + extra + (['-Xptxas', '-v'] if verbose else []) + \
           ['-o', LIB, os.path.join(HERE, 'unity.cu')]
     r = subprocess.run(cmd, capture_output=True, text=True)

@@ -204,7 +204,13 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     }
     // A CTA that allocates tensor memory must be alone on its SM (a second one would wait for the
     // columns): ask for more than half of the shared memory.
-    const size_t smem = (V & kVarTmem) ? std::max(lay.total(W), (size_t)max_smem / 2 + 1024) : lay.total(W);
+    size_t smem = (V & kVarTmem) ? std::max(lay.total(W), (size_t)max_smem / 2 + 1024) : lay.total(W);
+    if constexpr ((V & kVarSwDirect) != 0) {
+        // the exp table occupies shared-window addresses [0x10000, 0x20000): everything else has to end below
+        // 0x10000 (the window starts at a small driver-reserved offset), and the window has to reach 0x20000
+        if (lay.total(W) + 2048 > kXlWindow || (size_t)max_smem < 2 * (size_t)kXlWindow) return launch_flux<Real, MM, V & ~kVarSwDirect>(p, io, Tint, s);
+        smem = 2 * (size_t)kXlWindow;
+    }
     CMB_CUDA(cudaFuncSetAttribute(flux_kernel<Real, MM, V>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int ctas_per_sm = 1;
     CMB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, flux_kernel<Real, MM, V>, W * 32, smem));
@@ -302,6 +308,14 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     if (debug_timing) {
         CMB_CUDA(dbg.alloc(64));
         a.dbg = dbg.p;
+    }
+    if constexpr ((V & (kVarExpLds | kVarSwDirect)) != 0) {
+        if (!p->exp_tab.p) {      // 2^(j/512): exp2l in long double (64-bit significand), rounded once to double
+            std::vector<double> tab(kXlN);
+            for (int j = 0; j < kXlN; ++j) tab[j] = (double)exp2l((long double)j / kXlN);
+            CMB_CUDA(p->exp_tab.upload(tab.data(), tab.size()));
+        }
+        a.exp_tab = p->exp_tab.p;
     }
     a.tmem_cpw = tmem_cpw;
     a.tmem_cols = tmem_cols;
@@ -502,6 +516,18 @@ extern "C" int cmb200_flux(cmb200_plan *plan, const cmb200_flux_io *io, void *st
     const int variant = flux_variant();
 #define CMB_FLUX_CASE(REAL, M_) \
     case M_: return launch_flux_variant<REAL, M_>(variant, plan, io, Tint, s);
+#ifdef CMB_DEV_BUILD      /* kernel development: only the bench shapes, so that a rebuild takes seconds */
+    if (plan->precision == CMB200_F64) {
+        switch (mm) {
+            CMB_FLUX_CASE(double, 0)
+            CMB_FLUX_CASE(double, 2)
+        }
+    } else {
+        switch (mm) {
+            CMB_FLUX_CASE(float, 2)
+        }
+    }
+#else
     if (plan->precision == CMB200_F64) {
         switch (mm) {
             CMB_FLUX_CASE(double, 0)
@@ -519,6 +545,7 @@ extern "C" int cmb200_flux(cmb200_plan *plan, const cmb200_flux_io *io, void *st
             CMB_FLUX_CASE(float, 4)
         }
     }
+#endif
 #undef CMB_FLUX_CASE
     set_error("unsupported molecule count %d", mm);
     return CMB200_ERR_LIMIT;

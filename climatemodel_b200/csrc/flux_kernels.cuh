@@ -63,6 +63,7 @@ struct FluxArgs {
     unsigned long long *task_counter;   // zeroed before the launch
     long long *dbg;            // optional: sweep cycles per warp of CTA 0's first task (CMB200_DEBUG_TIMING)
     int tmem_cols, tmem_cpw;   // TMEM t-store: columns allocated per CTA, columns per warp (V & kVarTmem)
+    const double *exp_tab;     // [kXlN] 2^(j/512), correctly rounded (kVarExpLds)
     int seg_space;             // KL is the segment-space table (column = segment * 32 + lane), pitch its row length
     int tm_rows;               // layers of a warp's t-store kept in tensor memory (the rest in shared memory)
 };
@@ -84,7 +85,27 @@ struct FluxArgs {
 //                 instructions per layer instead of 15;
 //   kVarExpRegs   its constants are pinned in registers (a DFMA with a constant-bank operand issues
 //                 every 2.46 cycles instead of every 2, tools/issue_mix_microbench.cu).
+//   kVarExpLds    (FP64) exp(-x) = 2^n 2^(j/512) e^r with the 512-entry table of 2^(j/512) in shared memory,
+//                 replicated sixteen times so that lane l reads bank pair l & 15 whatever j it needs (no
+//                 conflicts), a one-FMA range reduction and e^r = 1 + r + r^2 (1/2 + r/6): 7 FP64
+//                 instructions per layer instead of 15, error <= 1e-14 where the parity gate is 1e-10;
+//   kVarTmPairs   (with kVarTmem) the t-store moves two layers (four 32-bit words) per LDTM / STTM instead
+//                 of a block of eight: no 16-register operand blocks, so ptxas needs no moves around them.
 constexpr int kVarTmem = 1, kVarCoefSmem = 2, kVarPartial = 4, kVarMixed = 8, kVarExpTable = 16, kVarExpRegs = 32;
+//   kVarSwDirect  (FP64, fused) short-wave fresh passes run sw_fresh_pass: every block is finished inside its own
+//                 iteration (stage 1, exp, both recurrences, t-store traffic), only the block's warp reduction
+//                 is carried into the next iteration; implies the shared-memory exp table at shared address
+//                 0x10000 (the CTA asks for 128 kB of dynamic shared memory).
+constexpr int kVarExpLds = 1024, kVarTmPairs = 2048, kVarSwDirect = 4096;
+constexpr unsigned kXlWindow = 0x10000u;                    // kVarSwDirect: shared-window address of the exp table
+constexpr int kXlN = 512, kXlLog = 9, kXlCopies = 16;       // table entries, log2, replicas
+// Per-warp handles of the exp tables: this lane's entry of the 2^(j/32) register table (kVarExpTable) and
+// the shared-memory table already offset by lane & 15 (kVarExpLds).
+struct ExpAux {
+    double tabT;
+    const double *lds;
+    unsigned saddr;       // kVarSwDirect: kXlWindow | (lane & 15) * 8
+};
 // Ablation switches for timing experiments only (results are wrong): skip the table loads after the
 // first block, the exp polynomial, the warp reduction, the t-store traffic.
 constexpr int kAblLoads = 64, kAblExp = 128, kAblReduce = 256, kAblTstore = 512;
@@ -151,6 +172,7 @@ struct CtaSmem {
     size_t off_offdn, off_offup, off_qg, off_hdp, shared_total, warp_bacc, warp_coef, warp_ts, warp_total;
     int lev_stride;
     // ts_rows: layers of the t-store a warp keeps in shared memory (-1: all of them, or none with kVarTmem)
+    size_t off_xtab;
     __host__ __device__ CtaSmem(int L, int ts_rows = -1) {
         auto up16 = [](size_t x) { return (x + 15) & ~(size_t)15; };
         const int Lp = padded_layers(L), MR = MM > 0 ? MM : 1;
@@ -165,6 +187,8 @@ struct CtaSmem {
         b = up16(b + (size_t)MR * lev_stride * sizeof(Real));
         off_hdp = b;
         b = up16(b + (size_t)Lp * sizeof(Real));
+        off_xtab = b;
+        if ((V & kVarExpLds) && !(V & kVarSwDirect)) b = up16(b + (size_t)kXlN * kXlCopies * sizeof(double));
         shared_total = b;
         // per warp: band accumulators (bacc_up, bacc_dn [Lp + kU] each, or the partial-sum layout
         // [2][Lp / 2][kPartialLanes][2]), the staged coefficient rows [4][Lp], the t-store [Lp][32]
@@ -371,13 +395,15 @@ template <typename Real, int MM, bool LW, bool UP, bool FRESH, int V>
 __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const int Lp, const Real wF, const Real wR,
                                            const Real b0, const void *src_lane, const void *next_src,
                                            PassFeed<Real, MM> &fd, const LevelView<Real> lv, const TStore<Real> tst,
-                                           double *bacc, const Real *coefL, const Real *coefG, const double tabT) {
+                                           double *bacc, const Real *coefL, const Real *coefG, const ExpAux xaux) {
     constexpr bool FUSED = MM > 0;
     constexpr int MR = MM > 0 ? MM : 1;
     constexpr bool F64 = sizeof(Real) == 8;
     constexpr bool TM = (V & kVarTmem) != 0, CS = (V & kVarCoefSmem) != 0, PA = (V & kVarPartial) != 0;
     constexpr bool MIX = TM && (V & kVarMixed) != 0;
     constexpr bool XT = F64 && (V & kVarExpTable) != 0, XR = XT && (V & kVarExpRegs) != 0;
+    constexpr bool XL = F64 && (V & kVarExpLds) != 0;
+    const double tabT = xaux.tabT;
     constexpr int WPR = sizeof(Real) / 4, NW = kU * WPR;   // 32-bit words per value / per block and lane
     using Src = typename std::conditional<FUSED, Real, double>::type;
     const char *src_bytes = (const char *)src_lane;
@@ -390,9 +416,18 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
     Real *const tsl = MIX ? tst.lane - tst.tm_rows * 32 : tst.lane;   // layer k sits at tsl[k * 32]
     // Tensor-memory modes: one block (kU layers) of the t-store <-> NW words per lane.  kVarMixed:
     // blocks below tm_rows are in tensor memory, the others in shared memory (warp-uniform branch).
+    constexpr int TG = (V & kVarTmPairs) ? 2 * WPR : 0;     // words per small LDTM / STTM: two layers
     auto ts_fetch = [&](int k0, uint32_t(&w)[NW]) {
         if constexpr ((V & kAblTstore) != 0) return;
-        if (!MIX || k0 < tst.tm_rows) {
+        if constexpr (TG != 0) {
+#pragma unroll
+            for (int g = 0; g < NW / TG; ++g) {
+                uint32_t q[TG];
+                tmem::ld_small<TG>(tst.taddr + (uint32_t)(k0 * WPR + g * TG), q);
+#pragma unroll
+                for (int i = 0; i < TG; ++i) w[g * TG + i] = q[i];
+            }
+        } else if (!MIX || k0 < tst.tm_rows) {
             tmem::ld<NW>(tst.taddr + (uint32_t)(k0 * WPR), w);
         } else {
             Real tmp[kU];
@@ -403,7 +438,17 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
     };
     auto ts_park = [&](int k0, const Real(&t)[kU]) {
         if constexpr ((V & kAblTstore) != 0) return;
-        if (!MIX || k0 < tst.tm_rows) {
+        if constexpr (TG != 0) {
+            uint32_t tw[NW];
+            tmem::pack<kU>(t, tw);
+#pragma unroll
+            for (int g = 0; g < NW / TG; ++g) {
+                uint32_t q[TG];
+#pragma unroll
+                for (int i = 0; i < TG; ++i) q[i] = tw[g * TG + i];
+                tmem::st_small<TG>(tst.taddr + (uint32_t)(k0 * WPR + g * TG), q);
+            }
+        } else if (!MIX || k0 < tst.tm_rows) {
             uint32_t tw[NW];
             tmem::pack<kU>(t, tw);
             tmem::st<NW>(tst.taddr + (uint32_t)(k0 * WPR), tw);
@@ -698,6 +743,57 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
                     }
                 }
                 if (DO_B) C4();
+            } else if constexpr (XL) {
+                // exp(-x) with the shared-memory 2^(j/512) table: n' = rint(-x 512/ln2) = 512 n + j,
+                // r = -x - n' ln2/512 (one FMA with the rounded constant: error <= n' 2^-63, below 1e-13
+                // for every x <= 708), t = 2^n T_j (1 + r + r^2 (1/2 + r/6)); step by step across the layers
+                constexpr double kK = 0x1.71547652b82fep+9, kMagic = 6755399441055744.0, kC = -0x1.62e42fefa39efp-10;
+                double tn[kU], r[kU], r2[kU], p[kU], Tj[kU];
+                int nn[kU];
+                if (DO_A) {
+#pragma unroll
+                    for (int u = 0; u < kU; ++u) {
+                        x[u] = clamp_thickness(x[u]);
+                        tn[u] = fma(-x[u], kK, kMagic);
+                    }
+                }
+                if (DO_B) { Bpair(kb, 0, v, knext); park(kb, 0); park(kb, 1); }
+                if (DO_A) {
+#pragma unroll
+                    for (int u = 0; u < kU; ++u) {
+                        nn[u] = __double2loint(tn[u]);
+                        tn[u] -= kMagic;
+                        Tj[u] = xaux.lds[(nn[u] & (kXlN - 1)) * kXlCopies];
+                    }
+                }
+                if (DO_B) { Bpair(kb, 1, v, knext); park(kb, 2); park(kb, 3); }
+                if (DO_A) {
+#pragma unroll
+                    for (int u = 0; u < kU; ++u) r[u] = fma(tn[u], kC, -x[u]);
+                }
+                if (DO_B) { Bpair(kb, 2, v, knext); park(kb, 4); park(kb, 5); }
+                if (DO_A) {
+#pragma unroll
+                    for (int u = 0; u < kU; ++u) {
+                        r2[u] = r[u] * r[u];
+                        p[u] = fma(r[u], 1.0 / 6.0, 0.5);
+                    }
+                }
+                if (DO_B) { Bpair(kb, 3, v, knext); park(kb, 6); park(kb, 7); C1(); }
+                if (DO_A) fetch_replay(k0);
+                if (DO_A) {
+#pragma unroll
+                    for (int u = 0; u < kU; ++u) p[u] = fma(r2[u], p[u], r[u]);
+                }
+                if (DO_B) { C2(); C3(); }
+                if (DO_A) {
+#pragma unroll
+                    for (int u = 0; u < kU; ++u) {
+                        const double tt = fma(Tj[u], p[u], Tj[u]);
+                        t[u] = __hiloint2double(__double2hiint(tt) + ((nn[u] >> kXlLog) << 20), __double2loint(tt));
+                    }
+                }
+                if (DO_B) { C4(); C5(); }
             } else if constexpr (F64) {
                 double tn[kU], r[kU], p[kU];
                 int n[kU];
@@ -883,12 +979,195 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
     }
 }
 
+// ---- short-wave fresh pass, direct form (kVarSwDirect) -----------------------------------------------
+// Integer helpers written as PTX so that ptxas keeps them on the ALU pipe in the shape intended.
+__device__ __forceinline__ double xl_lookup(int n, unsigned saddr_lane) {
+    // entry j = n & 511 of the replicated table: byte offset j * 128 inside the 64 kB window at 0x10000
+    unsigned s, a;
+    asm("shf.l.wrap.b32 %0, %1, %1, 7;" : "=r"(s) : "r"(n));
+    asm("lop3.b32 %0, %1, 0xff80, %2, 0xEA;" : "=r"(a) : "r"(s), "r"(saddr_lane));      // (s & 0xff80) | saddr_lane
+    double T;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(T) : "r"(a));
+    return T;
+}
+__device__ __forceinline__ double xl_scale(double tt, int n) {
+    // tt * 2^(n >> 9): the exponent field gets (n & ~511) * 2^11 = (n >> 9) << 20
+    int m, hi;
+    asm("and.b32 %0, %1, 0xfffffe00;" : "=r"(m) : "r"(n));
+    asm("mad.lo.s32 %0, %1, 2048, %2;" : "=r"(hi) : "r"(m), "r"(__double2hiint(tt)));
+    return __hiloint2double(hi, __double2loint(tt));
+}
+
+// One downward (UP = false) or upward pass of a short-wave segment pair: fresh chain of this segment (rows
+// src_lane, weight wF) and replay chain of the previous one (weight wR, its t read back from the t-store in
+// tensor memory).  Same conventions as sweep_pass (level tables, carried interface, t-store addressing, band
+// accumulators), but a block of kU layers is finished inside its iteration:
+//   table values of the block (loaded one block ahead) -> layer integrands -> thicknesses -> exp ->
+//   both recurrences -> park t;  then the next block's loads go out into the same registers.
+// Only the warp reduction of the block's eight values is carried: it is interleaved with the next block's
+// exp (its five shuffle stages are a ~160-cycle dependent chain).
+template <int MM, bool UP, int V>
+__device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, const int Lp, const double wF, const double wR,
+                                              const double b0, const void *src_lane, const void *next_src,
+                                              PassFeed<double, MM> &fd, const LevelView<double> lv,
+                                              const TStore<double> tst, double *bacc, const ExpAux xaux) {
+    static_assert(MM > 0, "table-fused path");
+    constexpr int NW = 2 * kU;
+    constexpr double kK = 0x1.71547652b82fep+9, kMagic = 6755399441055744.0, kC = -0x1.62e42fefa39efp-10;
+    const unsigned full = 0xffffffffu;
+    const bool h4 = lane & 16, h3 = lane & 8, h2 = lane & 4;
+    const int ridx = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+    const bool rlane = (lane & 3) == 0;
+    const int kfirst = UP ? Lp - kU : 0, kstep = UP ? -kU : kU;
+    const char *src_bytes = (const char *)src_lane;
+    const unsigned *offs = UP ? lv.off_up : lv.off_dn;
+    auto &raw = fd.raw;
+
+    double EF = wF * b0, ER = wR * b0;
+    double Ic = 0.0;
+#pragma unroll
+    for (int m = 0; m < MM; ++m) Ic = fma(lv.qg[m * lv.stride + (UP ? Lp : 0) + kLevShift], fd.icraw[m], Ic);
+
+    double v[kU], a4[4], a2[2], c1 = 0.0;
+#pragma unroll
+    for (int u = 0; u < kU; ++u) v[u] = 0.0;
+    int kprev = -kU * 4;        // block whose values v holds (none yet: its accumulate is predicated off)
+
+    for (int it = 0, k0 = kfirst; it < Lp / kU; ++it, k0 += kstep) {
+        const bool last = it == Lp / kU - 1;
+        // replay chain's t of this block
+        uint32_t tRw[NW];
+        if constexpr ((V & kAblTstore) == 0) {
+            tmem::ld<NW>(tst.taddr + (uint32_t)(k0 * 2), tRw);
+        } else {
+#pragma unroll
+            for (int i = 0; i < NW; ++i) tRw[i] = 0x3ff00000u * (i & 1);
+        }
+        // band accumulator of the block being reduced (read early, written at the end)
+        double bold = 0.0;
+        const bool acc_on = rlane && kprev >= 0 && kprev + ridx < nl;
+        if (acc_on) bold = bacc[kprev + ridx];
+
+        // ---- stage 1: integrand at the block's loaded interfaces, thickness of its layers ------------
+        double In[kU], x[kU];
+#pragma unroll
+        for (int m = 0; m < MM; ++m) {
+            double qg[kU];
+            if (UP)
+                lds_block_m1(lv.qg + m * lv.stride + k0 + kLevShift, qg);
+            else
+                lds_block(lv.qg + m * lv.stride + k0 + 1 + kLevShift, qg);
+#pragma unroll
+            for (int u = 0; u < kU; ++u) In[u] = m ? fma(qg[u], raw[u][m], In[u]) : qg[u] * raw[u][0];
+        }
+        {
+            double hd[kU];
+            lds_block(lv.hdp + k0, hd);
+#pragma unroll
+            for (int u = 0; u < kU; ++u) {
+                const double lo = UP ? In[u] : (u ? In[u - 1] : Ic);
+                const double hi = UP ? (u < kU - 1 ? In[u + 1] : Ic) : In[u];
+                x[u] = hd[u] * (lo + hi);
+            }
+            Ic = UP ? In[0] : In[kU - 1];
+        }
+        // ---- the next block's table values (or the next pass's first block) into the same registers ----
+        if constexpr ((V & kAblLoads) != 0) {
+        } else if (!last) {
+#pragma unroll
+            for (int m = 0; m < MM; ++m) {
+                unsigned off[kU];
+                lds_block(offs + m * lv.stride + k0 + kstep + 4, off);
+#pragma unroll
+                for (int u = 0; u < kU; ++u) raw[u][m] = *(const double *)(src_bytes + (size_t)off[u] * 16u);
+            }
+        } else if (next_src) {
+            prefetch_pass<double, MM>(!UP, Lp, next_src, lv, fd);
+        }
+
+        // ---- exp of the block's eight layers, with the previous block's reduction in between ----------
+        double tn[kU], r[kU], r2[kU], p[kU], Tj[kU], t[kU];
+        int nn[kU];
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+            int hi = __double2hiint(x[u]);
+            asm("min.s32 %0, %0, 0x40862000;" : "+r"(hi));            // thickness clamp (clamp_thickness), in place
+            x[u] = __hiloint2double(hi, __double2loint(x[u]));
+            tn[u] = fma(-x[u], kK, kMagic);
+        }
+        constexpr bool RED = (V & kAblReduce) == 0, XP = (V & kAblExp) == 0;
+        if constexpr (!RED) c1 = ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
+        if constexpr (RED)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {                                    // reduction step 1 (xor 16)
+            const double keep = h4 ? v[i + 4] : v[i], send = h4 ? v[i] : v[i + 4];
+            a4[i] = keep + __shfl_xor_sync(full, send, 16);
+        }
+        if constexpr (XP)
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+            nn[u] = __double2loint(tn[u]);
+            tn[u] -= kMagic;
+            Tj[u] = xl_lookup(nn[u], xaux.saddr);
+        }
+        if constexpr (XP)
+#pragma unroll
+        for (int u = 0; u < kU; ++u) r[u] = fma(tn[u], kC, -x[u]);
+        if constexpr (RED)
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {                                    // step 2 (xor 8)
+            const double keep = h3 ? a4[i + 2] : a4[i], send = h3 ? a4[i] : a4[i + 2];
+            a2[i] = keep + __shfl_xor_sync(full, send, 8);
+        }
+        if constexpr (XP)
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+            r2[u] = r[u] * r[u];
+            p[u] = fma(r[u], 1.0 / 6.0, 0.5);
+        }
+        if constexpr (RED) {                                             // step 3 (xor 4)
+            const double keep = h2 ? a2[1] : a2[0], send = h2 ? a2[0] : a2[1];
+            c1 = keep + __shfl_xor_sync(full, send, 4);
+        }
+        if constexpr (XP)
+#pragma unroll
+        for (int u = 0; u < kU; ++u) p[u] = fma(r2[u], p[u], r[u]);
+        if constexpr (RED) c1 += __shfl_xor_sync(full, c1, 2);           // step 4
+#pragma unroll
+        for (int u = 0; u < kU; ++u) t[u] = XP ? xl_scale(fma(Tj[u], p[u], Tj[u]), nn[u]) : tn[u];
+        if constexpr (RED) c1 += __shfl_xor_sync(full, c1, 1);           // step 5
+
+        // ---- both recurrences in sweep order; the block's values for the next iteration's reduction ---
+        double tR[kU];
+        if constexpr ((V & kAblTstore) == 0) tmem::wait_ld<NW>(tRw);
+        tmem::unpack<kU>(tRw, tR);
+#pragma unroll
+        for (int o = 0; o < kU; ++o) {
+            const int u = UP ? kU - 1 - o : o;
+            EF *= t[u];
+            ER *= tR[u];
+            v[u] = EF + ER;
+        }
+        if constexpr ((V & kAblTstore) == 0) {
+            uint32_t tw[NW];
+            tmem::pack<kU>(t, tw);
+            tmem::st<NW>(tst.taddr + (uint32_t)(k0 * 2), tw);
+        }
+        if (acc_on) bacc[kprev + ridx] = bold + c1;
+        kprev = k0;
+    }
+    // ---- reduction of the last block ------------------------------------------------------------------
+    const double c = reduce8<double>(v, lane);
+    if (rlane && kprev + ridx < nl) bacc[kprev + ridx] += c;
+    tmem::wait_st();
+}
+
 template <typename Real, int MM, bool FRESH, int V>
 __device__ __forceinline__ void dispatch_pass(const bool lw, const bool up, const int lane, const int nl, const int Lp,
                                               const Real wF, const Real wR, const Real bs, const Real bg,
                                               const void *src_lane, const void *next_src, PassFeed<Real, MM> &fd,
                                               const LevelView<Real> &lv, const TStore<Real> tst, double *bacc_up, double *bacc_dn,
-                                              const Real *coef, const double tabT) {
+                                              const Real *coef, const ExpAux tabT) {
     // coefficient rows of a band: [0] dn_last, [1] dn_gen, [2] up_first, [3] up_gen.  The value of layer k
     // of a downward pass belongs to interface k + 1: the plain accumulators are indexed by interface, the
     // partial-sum accumulators (kVarPartial) by layer.
@@ -899,7 +1178,12 @@ __device__ __forceinline__ void dispatch_pass(const bool lw, const bool up, cons
         else
             sweep_pass<Real, MM, true, false, FRESH, V>(lane, nl, Lp, wF, wR, bs, src_lane, next_src, fd, lv, tst, dn, coef, coef + Lp, tabT);
     } else {
-        if (up)
+        if constexpr (FRESH && MM > 0 && sizeof(Real) == 8 && (V & kVarSwDirect) != 0) {
+            if (up)
+                sw_fresh_pass<MM, true, V>(lane, nl, Lp, wF, wR, bg, src_lane, next_src, fd, lv, tst, bacc_up, tabT);
+            else
+                sw_fresh_pass<MM, false, V>(lane, nl, Lp, wF, wR, bs, src_lane, next_src, fd, lv, tst, dn, tabT);
+        } else if (up)
             sweep_pass<Real, MM, false, true, FRESH, V>(lane, nl, Lp, wF, wR, bg, src_lane, next_src, fd, lv, tst, bacc_up, coef, coef, tabT);
         else
             sweep_pass<Real, MM, false, false, FRESH, V>(lane, nl, Lp, wF, wR, bs, src_lane, next_src, fd, lv, tst, dn, coef, coef, tabT);
@@ -941,7 +1225,13 @@ __global__ void __launch_bounds__(variant_threads(V), 1) flux_kernel(const FluxA
     // The t-store: the first replay of a run reads it with weight 0, so it has to hold finite numbers.
     __shared__ uint32_t s_tmem_base;
     TStore<Real> tst{ts + lane, 0u, a.tm_rows};
-    const double tabT = kExpTab[lane];             // this lane's entry of the 2^(j/32) table (kVarExpTable)
+    // exp tables: this lane's entry of the 2^(j/32) table (kVarExpTable); the replicated 2^(j/512) table (kVarExpLds)
+    double *xtab = (double *)(smem_raw + lay.off_xtab);
+    if constexpr ((V & kVarSwDirect) != 0)      // the table sits at shared-window address kXlWindow (launch_flux sizes the window)
+        xtab = (double *)(smem_raw + (kXlWindow - (unsigned)__cvta_generic_to_shared(smem_raw)));
+    if constexpr ((V & (kVarExpLds | kVarSwDirect)) != 0)
+        for (int i = tid; i < kXlN * kXlCopies; i += nthr) xtab[i] = a.exp_tab[i / kXlCopies];
+    const ExpAux tabT{kExpTab[lane], xtab + (lane & (kXlCopies - 1)), kXlWindow | ((unsigned)(lane & (kXlCopies - 1)) << 3)};
     if constexpr (TM) {
         if (warp == 0) tmem::acquire(&s_tmem_base, (uint32_t)a.tmem_cols);
         tmem::fence_before_sync();

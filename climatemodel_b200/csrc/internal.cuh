@@ -81,6 +81,7 @@ struct cmb200_plan {
     cmb::DevBuf<double> Tint, scratch, coefbuf;
     cmb::DevBuf<uint8_t> tidx;
     cmb::DevBuf<unsigned long long> task_counter;
+    cmb::DevBuf<double> exp_tab;        // 2^(j/512), the flux kernel's shared-memory exp table (kVarExpLds)
     cmb200_host_pipe *host_pipe = nullptr;   // streams and staging buffers of cmb200_flux_host
     ~cmb200_plan() {
         if (host_pipe) cmb::destroy_host_pipe(host_pipe);

@@ -78,6 +78,47 @@ __device__ __forceinline__ void st(uint32_t addr, const uint32_t (&r)[NW]) {
     }
 }
 
+// Two or four consecutive columns per lane (one or two FP64 values): small operand groups that ptxas can
+// keep in the registers the values already live in.
+template <int NW>
+__device__ __forceinline__ void ld_small(uint32_t addr, uint32_t (&r)[NW]) {
+    static_assert(NW == 2 || NW == 4, "2 or 4 columns");
+    if constexpr (NW == 4) {
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+                     : "r"(addr));
+    } else {
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0, %1}, [%2];" : "=r"(r[0]), "=r"(r[1]) : "r"(addr));
+    }
+}
+template <int NW>
+__device__ __forceinline__ void st_small(uint32_t addr, const uint32_t (&r)[NW]) {
+    static_assert(NW == 2 || NW == 4, "2 or 4 columns");
+    if constexpr (NW == 4) {
+        asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]) : "memory");
+    } else {
+        asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1, %2};" ::"r"(addr), "r"(r[0]), "r"(r[1]) : "memory");
+    }
+}
+// Wait for every outstanding tcgen05.ld of the thread; the loaded words are in-out operands so that no
+// use is scheduled before the wait.
+template <int NW>
+__device__ __forceinline__ void wait_ld_all(uint32_t (&r)[NW]) {
+    static_assert(NW == 16 || NW == 8, "a block of words");
+    if constexpr (NW == 16) {
+        asm volatile("tcgen05.wait::ld.sync.aligned;"
+                     : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                       "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15])
+                     :
+                     : "memory");
+    } else {
+        asm volatile("tcgen05.wait::ld.sync.aligned;"
+                     : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7])
+                     :
+                     : "memory");
+    }
+}
+
 // kU reals <-> 32-bit words (register renames, no instructions).
 template <int N>
 __device__ __forceinline__ void pack(const double (&v)[N], uint32_t (&w)[2 * N]) {
