@@ -144,13 +144,21 @@ static int variant_warps(int L, int max_smem, int *tmem_cpw, int *tmem_cols, int
 // the default one; further variants are experiments, compiled for FP64 with 0 or 2 molecules only
 // when the build names them (CMB200_EXPERIMENTS="17,21" python -m climatemodel_b200.csrc.build) and
 // selected at run time with CMB200_FLUX_VARIANT (tools/ab_flux_variants.py).
-constexpr int kDefaultVariant = kVarTmem | kVarCoefSmem;
+// Default variant per arithmetic type and optical-depth source: FP32 and the reference FP64 variant keep the
+// round-1 kernel (t-store in tensor memory, staged coefficient rows; bit-identical to the plain kernel 0);
+// FP64 adds the shared-memory exp table and, on the table-fused path, the direct short-wave pass.
+constexpr int kReferenceVariant = kVarTmem | kVarCoefSmem;
+template <typename Real, int MM>
+constexpr int default_variant() {
+    if (!std::is_same<Real, double>::value) return kReferenceVariant;
+    return MM > 0 ? (kReferenceVariant | kVarExpLds | kVarSwDirect) : (kReferenceVariant | kVarExpLds);
+}
 #ifndef CMB_FLUX_EXPERIMENTS
 #define CMB_FLUX_EXPERIMENTS(X)
 #endif
-static int flux_variant() {
+static int flux_variant() {          // -1: the default of the (type, source) at hand
     const char *e = getenv("CMB200_FLUX_VARIANT");
-    return e && *e ? atoi(e) : kDefaultVariant;
+    return e && *e ? atoi(e) : -1;
 }
 
 // The level table regathered into segment space (internal.cuh) for the fused path; CMB200_SEGMENT_TABLE=0
@@ -208,8 +216,13 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     if constexpr ((V & kVarSwDirect) != 0) {
         // the exp table occupies shared-window addresses [0x10000, 0x20000): everything else has to end below
         // 0x10000 (the window starts at a small driver-reserved offset), and the window has to reach 0x20000
-        if (lay.total(W) + 2048 > kXlWindow || (size_t)max_smem < 2 * (size_t)kXlWindow) return launch_flux<Real, MM, V & ~kVarSwDirect>(p, io, Tint, s);
+        if (lay.total(W) + 2048 > kXlWindow || (size_t)max_smem < 2 * (size_t)kXlWindow)
+            return launch_flux<Real, MM, V & ~(kVarSwDirect | kVarRedSmem)>(p, io, Tint, s);
         smem = 2 * (size_t)kXlWindow;
+        if constexpr ((V & kVarRedSmem) != 0) {      // group accumulators and exchange scratch of every warp above the table
+            smem += (size_t)W * red_warp_bytes(Lp);
+            if (smem > (size_t)max_smem) return launch_flux<Real, MM, V & ~kVarRedSmem>(p, io, Tint, s);
+        }
     }
     CMB_CUDA(cudaFuncSetAttribute(flux_kernel<Real, MM, V>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int ctas_per_sm = 1;
@@ -372,7 +385,8 @@ static int launch_flux_variant(int variant, cmb200_plan *plan, const cmb200_flux
 #undef CMB_FLUX_X
     }
     if (variant == 0) return launch_flux<Real, MM, 0>(plan, io, Tint, s);
-    return launch_flux<Real, MM, kDefaultVariant>(plan, io, Tint, s);
+    if (variant == kReferenceVariant) return launch_flux<Real, MM, kReferenceVariant>(plan, io, Tint, s);
+    return launch_flux<Real, MM, default_variant<Real, MM>()>(plan, io, Tint, s);
 }
 
 static int validate_flux_io(const cmb200_plan *p, const cmb200_flux_io *io) {
@@ -708,7 +722,7 @@ extern "C" int cmb200_test_exp_neg_host(const double *x, int64_t n, double *out)
     DevBuf<double> dx, dout;
     CMB_CUDA(dx.upload(x, n));
     CMB_CUDA(dout.alloc(n));
-    exp_neg_test_kernel<<<(unsigned)((n + 255) / 256), 256>>>(dx.p, n, dout.p, (flux_variant() & kVarExpTable) != 0);
+    exp_neg_test_kernel<<<(unsigned)((n + 255) / 256), 256>>>(dx.p, n, dout.p, flux_variant() > 0 && (flux_variant() & kVarExpTable) != 0);
     CMB_LAUNCHED();
     CMB_CUDA(cudaMemcpy(out, dout.p, n * sizeof(double), cudaMemcpyDeviceToHost));
     return CMB200_OK;

@@ -96,7 +96,25 @@ constexpr int kVarTmem = 1, kVarCoefSmem = 2, kVarPartial = 4, kVarMixed = 8, kV
 //                 iteration (stage 1, exp, both recurrences, t-store traffic), only the block's warp reduction
 //                 is carried into the next iteration; implies the shared-memory exp table at shared address
 //                 0x10000 (the CTA asks for 128 kB of dynamic shared memory).
-constexpr int kVarExpLds = 1024, kVarTmPairs = 2048, kVarSwDirect = 4096;
+//   kVarRedSmem   (with kVarSwDirect) the warp reduction of a block's eight values goes through shared memory
+//                 instead of 18 shuffles + 28 selects: every lane parks its eight values in its row of a
+//                 per-warp scratch (4 STS.128), lane (g, c) = (lane >> 3, lane & 7) adds the values of layer c
+//                 from the eight rows of lane group g (8 conflict-free LDS.64) and keeps the result in ITS OWN
+//                 band accumulator b4[g][layer] -- the four group accumulators are added when the (warp, band)
+//                 run is written out.  Short-wave replay-only passes take the same route (sw_replay_pass).
+//   kVarSwPoly    (with kVarSwDirect) sw_fresh_pass evaluates exp with the degree-11 polynomial (15 FP64
+//                 instructions, no shared-memory lookup) instead of the table routine.
+constexpr int kVarExpLds = 1024, kVarTmPairs = 2048, kVarSwDirect = 4096, kVarRedSmem = 8192, kVarSwPoly = 16384;
+constexpr int kRedStride = 18;                              // doubles per scratch row (144 B: 16-byte slots rotate over the banks)
+// Group accumulators of kVarRedSmem: [2 directions][4 lane groups][LS4] doubles, LS4 * 8 = 64 (mod 128) so
+// that the two groups of a half-warp fall into different banks.
+__host__ __device__ inline int red_ls4(int Lp) { return (Lp % 16 == 8) ? Lp : Lp + 8; }
+__host__ __device__ inline size_t red_warp_bytes(int Lp) { return (size_t)2 * 4 * red_ls4(Lp) * 8 + (size_t)32 * kRedStride * 8; }
+struct RedAux {
+    double *up_lane, *dn_lane;      // this lane's slot of the group accumulators at layer 0: b4[dir][g] + c
+    double *st_row;                 // scratch row of this lane
+    const double *ld_col;           // scratch element (first row of this lane's group, column c)
+};
 constexpr unsigned kXlWindow = 0x10000u;                    // kVarSwDirect: shared-window address of the exp table
 constexpr int kXlN = 512, kXlLog = 9, kXlCopies = 16;       // table entries, log2, replicas
 // Per-warp handles of the exp tables: this lane's entry of the 2^(j/32) register table (kVarExpTable) and
@@ -979,6 +997,54 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
     }
 }
 
+// kVarRedSmem: park the block's values, then fetch the eight partials this lane adds (row offsets are
+// compile-time).  Rows of group g = 2 g1 + g0: 8 (2 g1 + a) + 4 g0 + b, a < 2, b < 4 -- the two groups of a
+// half-warp read rows 4 apart, i.e. 64 bytes apart modulo the 128-byte bank row.
+__device__ __forceinline__ void red_exchange(const double (&v)[kU], const RedAux &ra, double (&part)[kU]) {
+    __syncwarp();                                   // everyone has read the previous block's rows
+#pragma unroll
+    for (int i = 0; i < kU / 2; ++i) reinterpret_cast<double2 *>(ra.st_row)[i] = make_double2(v[2 * i], v[2 * i + 1]);
+    __syncwarp();
+#pragma unroll
+    for (int j = 0; j < kU; ++j) part[j] = ra.ld_col[(8 * (j >> 2) + (j & 3)) * kRedStride];
+}
+__device__ __forceinline__ void red_accumulate(const double (&part)[kU], double *slot) {
+    const double s = ((part[0] + part[1]) + (part[2] + part[3])) + ((part[4] + part[5]) + (part[6] + part[7]));
+    *slot += s;
+}
+
+// Replay-only pass of a short-wave band run (the last segment's chain in the direction it has not been swept
+// in yet): ER *= t read back from the t-store, values reduced through shared memory like sw_fresh_pass.
+template <bool UP>
+__device__ __forceinline__ void sw_replay_pass(const int Lp, const double wR, const double b0, const TStore<double> tst,
+                                               const RedAux ra) {
+    constexpr int NW = 2 * kU;
+    const int kfirst = UP ? Lp - kU : 0, kstep = UP ? -kU : kU;
+    double ER = wR * b0;
+    double part[kU];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) part[u] = 0.0;
+    double *slot = UP ? ra.up_lane : ra.dn_lane;    // the first accumulate adds zeros to layer 0 + c
+    uint32_t tw[NW];
+    tmem::ld<NW>(tst.taddr + (uint32_t)(kfirst * 2), tw);
+    for (int it = 0, k0 = kfirst; it < Lp / kU; ++it, k0 += kstep) {
+        double tR[kU], v[kU];
+        tmem::wait_ld<NW>(tw);
+        tmem::unpack<kU>(tw, tR);
+        if (it + 1 < Lp / kU) tmem::ld<NW>(tst.taddr + (uint32_t)((k0 + kstep) * 2), tw);
+        red_accumulate(part, slot);
+#pragma unroll
+        for (int o = 0; o < kU; ++o) {
+            const int u = UP ? kU - 1 - o : o;
+            ER *= tR[u];
+            v[u] = ER;
+        }
+        red_exchange(v, ra, part);
+        slot = (UP ? ra.up_lane : ra.dn_lane) + k0;
+    }
+    red_accumulate(part, slot);
+}
+
 // ---- short-wave fresh pass, direct form (kVarSwDirect) -----------------------------------------------
 // Integer helpers written as PTX so that ptxas keeps them on the ALU pipe in the shape intended.
 __device__ __forceinline__ double xl_lookup(int n, unsigned saddr_lane) {
@@ -1010,8 +1076,9 @@ template <int MM, bool UP, int V>
 __device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, const int Lp, const double wF, const double wR,
                                               const double b0, const void *src_lane, const void *next_src,
                                               PassFeed<double, MM> &fd, const LevelView<double> lv,
-                                              const TStore<double> tst, double *bacc, const ExpAux xaux) {
+                                              const TStore<double> tst, double *bacc, const ExpAux xaux, const RedAux ra) {
     static_assert(MM > 0, "table-fused path");
+    constexpr bool RS = (V & kVarRedSmem) != 0;
     constexpr int NW = 2 * kU;
     constexpr double kK = 0x1.71547652b82fep+9, kMagic = 6755399441055744.0, kC = -0x1.62e42fefa39efp-10;
     const unsigned full = 0xffffffffu;
@@ -1032,6 +1099,10 @@ __device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, cons
 #pragma unroll
     for (int u = 0; u < kU; ++u) v[u] = 0.0;
     int kprev = -kU * 4;        // block whose values v holds (none yet: its accumulate is predicated off)
+    double part[kU];            // kVarRedSmem: the eight partials of the previous block, and where their sum goes
+#pragma unroll
+    for (int u = 0; u < kU; ++u) part[u] = 0.0;
+    double *slot = UP ? ra.up_lane : ra.dn_lane;
 
     for (int it = 0, k0 = kfirst; it < Lp / kU; ++it, k0 += kstep) {
         const bool last = it == Lp / kU - 1;
@@ -1045,8 +1116,9 @@ __device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, cons
         }
         // band accumulator of the block being reduced (read early, written at the end)
         double bold = 0.0;
-        const bool acc_on = rlane && kprev >= 0 && kprev + ridx < nl;
+        const bool acc_on = !RS && rlane && kprev >= 0 && kprev + ridx < nl;
         if (acc_on) bold = bacc[kprev + ridx];
+        if constexpr (RS) red_accumulate(part, slot);
 
         // ---- stage 1: integrand at the block's loaded interfaces, thickness of its layers ------------
         double In[kU], x[kU];
@@ -1086,7 +1158,65 @@ __device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, cons
         }
 
         // ---- exp of the block's eight layers, with the previous block's reduction in between ----------
-        double tn[kU], r[kU], r2[kU], p[kU], Tj[kU], t[kU];
+        double t[kU];
+        constexpr bool RED = (V & kAblReduce) == 0 && !RS;
+        if constexpr ((V & kVarSwPoly) != 0) {
+            double tn[kU], r[kU], p[kU];
+            int n[kU];
+#pragma unroll
+            for (int u = 0; u < kU; ++u) {
+                int hi = __double2hiint(x[u]);
+                asm("min.s32 %0, %0, 0x40862000;" : "+r"(hi));
+                x[u] = __hiloint2double(hi, __double2loint(x[u]));
+                tn[u] = fma(-x[u], kExpC[11], kExpC[12]);
+            }
+            if constexpr (RED)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const double keep = h4 ? v[i + 4] : v[i], send = h4 ? v[i] : v[i + 4];
+                a4[i] = keep + __shfl_xor_sync(full, send, 16);
+            }
+#pragma unroll
+            for (int u = 0; u < kU; ++u) {
+                n[u] = __double2loint(tn[u]);
+                tn[u] -= kExpC[12];
+            }
+#pragma unroll
+            for (int u = 0; u < kU; ++u) r[u] = fma(tn[u], kExpC[13], -x[u]);
+#pragma unroll
+            for (int u = 0; u < kU; ++u) {
+                r[u] = fma(tn[u], kExpC[14], r[u]);
+                p[u] = kExpC[0];
+            }
+#pragma unroll
+            for (int i = 1; i <= 10; ++i) {
+#pragma unroll
+                for (int u = 0; u < kU; ++u) p[u] = fma(p[u], r[u], kExpC[i]);
+                if constexpr (RED) {
+                    if (i == 2) {
+#pragma unroll
+                        for (int q = 0; q < 2; ++q) {
+                            const double keep = h3 ? a4[q + 2] : a4[q], send = h3 ? a4[q] : a4[q + 2];
+                            a2[q] = keep + __shfl_xor_sync(full, send, 8);
+                        }
+                    }
+                    if (i == 4) {
+                        const double keep = h2 ? a2[1] : a2[0], send = h2 ? a2[0] : a2[1];
+                        c1 = keep + __shfl_xor_sync(full, send, 4);
+                    }
+                    if (i == 6) c1 += __shfl_xor_sync(full, c1, 2);
+                    if (i == 8) c1 += __shfl_xor_sync(full, c1, 1);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < kU; ++u) {
+                p[u] = fma(p[u], r[u], kExpC[10]);
+                int hi;
+                asm("mad.lo.s32 %0, %1, 1048576, %2;" : "=r"(hi) : "r"(n[u]), "r"(__double2hiint(p[u])));
+                t[u] = __hiloint2double(hi, __double2loint(p[u]));
+            }
+        } else {
+        double tn[kU], r[kU], r2[kU], p[kU], Tj[kU];
         int nn[kU];
 #pragma unroll
         for (int u = 0; u < kU; ++u) {
@@ -1095,8 +1225,8 @@ __device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, cons
             x[u] = __hiloint2double(hi, __double2loint(x[u]));
             tn[u] = fma(-x[u], kK, kMagic);
         }
-        constexpr bool RED = (V & kAblReduce) == 0, XP = (V & kAblExp) == 0;
-        if constexpr (!RED) c1 = ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
+        constexpr bool XP = (V & kAblExp) == 0;
+        if constexpr (!RED && !RS) c1 = ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
         if constexpr (RED)
 #pragma unroll
         for (int i = 0; i < 4; ++i) {                                    // reduction step 1 (xor 16)
@@ -1137,6 +1267,8 @@ __device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, cons
         for (int u = 0; u < kU; ++u) t[u] = XP ? xl_scale(fma(Tj[u], p[u], Tj[u]), nn[u]) : tn[u];
         if constexpr (RED) c1 += __shfl_xor_sync(full, c1, 1);           // step 5
 
+        }
+
         // ---- both recurrences in sweep order; the block's values for the next iteration's reduction ---
         double tR[kU];
         if constexpr ((V & kAblTstore) == 0) tmem::wait_ld<NW>(tRw);
@@ -1155,10 +1287,18 @@ __device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, cons
         }
         if (acc_on) bacc[kprev + ridx] = bold + c1;
         kprev = k0;
+        if constexpr (RS) {
+            red_exchange(v, ra, part);
+            slot = (UP ? ra.up_lane : ra.dn_lane) + k0;
+        }
     }
     // ---- reduction of the last block ------------------------------------------------------------------
-    const double c = reduce8<double>(v, lane);
-    if (rlane && kprev + ridx < nl) bacc[kprev + ridx] += c;
+    if constexpr (RS) {
+        red_accumulate(part, slot);
+    } else {
+        const double c = reduce8<double>(v, lane);
+        if (rlane && kprev + ridx < nl) bacc[kprev + ridx] += c;
+    }
     tmem::wait_st();
 }
 
@@ -1167,7 +1307,7 @@ __device__ __forceinline__ void dispatch_pass(const bool lw, const bool up, cons
                                               const Real wF, const Real wR, const Real bs, const Real bg,
                                               const void *src_lane, const void *next_src, PassFeed<Real, MM> &fd,
                                               const LevelView<Real> &lv, const TStore<Real> tst, double *bacc_up, double *bacc_dn,
-                                              const Real *coef, const ExpAux tabT) {
+                                              const Real *coef, const ExpAux tabT, const RedAux ra) {
     // coefficient rows of a band: [0] dn_last, [1] dn_gen, [2] up_first, [3] up_gen.  The value of layer k
     // of a downward pass belongs to interface k + 1: the plain accumulators are indexed by interface, the
     // partial-sum accumulators (kVarPartial) by layer.
@@ -1180,9 +1320,15 @@ __device__ __forceinline__ void dispatch_pass(const bool lw, const bool up, cons
     } else {
         if constexpr (FRESH && MM > 0 && sizeof(Real) == 8 && (V & kVarSwDirect) != 0) {
             if (up)
-                sw_fresh_pass<MM, true, V>(lane, nl, Lp, wF, wR, bg, src_lane, next_src, fd, lv, tst, bacc_up, tabT);
+                sw_fresh_pass<MM, true, V>(lane, nl, Lp, wF, wR, bg, src_lane, next_src, fd, lv, tst, bacc_up, tabT, ra);
             else
-                sw_fresh_pass<MM, false, V>(lane, nl, Lp, wF, wR, bs, src_lane, next_src, fd, lv, tst, dn, tabT);
+                sw_fresh_pass<MM, false, V>(lane, nl, Lp, wF, wR, bs, src_lane, next_src, fd, lv, tst, dn, tabT, ra);
+        } else if constexpr (!FRESH && MM > 0 && sizeof(Real) == 8 && (V & kVarSwDirect) != 0 && (V & kVarRedSmem) != 0) {
+            if (next_src) prefetch_pass<Real, MM>(!up, Lp, next_src, lv, fd);
+            if (up)
+                sw_replay_pass<true>(Lp, (double)wR, (double)bg, *reinterpret_cast<const TStore<double> *>(&tst), ra);
+            else
+                sw_replay_pass<false>(Lp, (double)wR, (double)bs, *reinterpret_cast<const TStore<double> *>(&tst), ra);
         } else if (up)
             sweep_pass<Real, MM, false, true, FRESH, V>(lane, nl, Lp, wF, wR, bg, src_lane, next_src, fd, lv, tst, bacc_up, coef, coef, tabT);
         else
@@ -1232,6 +1378,21 @@ __global__ void __launch_bounds__(variant_threads(V), 1) flux_kernel(const FluxA
     if constexpr ((V & (kVarExpLds | kVarSwDirect)) != 0)
         for (int i = tid; i < kXlN * kXlCopies; i += nthr) xtab[i] = a.exp_tab[i / kXlCopies];
     const ExpAux tabT{kExpTab[lane], xtab + (lane & (kXlCopies - 1)), kXlWindow | ((unsigned)(lane & (kXlCopies - 1)) << 3)};
+    // kVarRedSmem: this warp's group accumulators and exchange scratch, above the exp table in the shared window
+    constexpr bool RS = (V & kVarRedSmem) != 0;
+    RedAux ra{nullptr, nullptr, nullptr, nullptr};
+    double *b4 = nullptr;
+    const int LS4 = red_ls4(Lp);
+    if constexpr (RS) {
+        b4 = (double *)(smem_raw + (2 * kXlWindow - (unsigned)__cvta_generic_to_shared(smem_raw)) + (size_t)warp * red_warp_bytes(Lp));
+        double *red = b4 + 8 * LS4;
+        const int g = lane >> 3, c = lane & 7;
+        ra.up_lane = b4 + g * LS4 + c;
+        ra.dn_lane = b4 + (4 + g) * LS4 + c;
+        ra.st_row = red + lane * kRedStride;
+        ra.ld_col = red + (16 * (g >> 1) + 4 * (g & 1)) * kRedStride + c;
+        for (int i = lane; i < 8 * LS4 + 32 * kRedStride; i += 32) b4[i] = 0.0;
+    }
     if constexpr (TM) {
         if (warp == 0) tmem::acquire(&s_tmem_base, (uint32_t)a.tmem_cols);
         tmem::fence_before_sync();
@@ -1387,12 +1548,12 @@ __global__ void __launch_bounds__(variant_threads(V), 1) flux_kernel(const FluxA
                 const void *src_lane = srcN;
                 if (s + 1 < s1) seg_params(s + 1, wN, srcN);
                 dispatch_pass<Real, MM, true, V>(lw, up, lane, nl, Lp, wF, wR, bs, bg, src_lane, s + 1 < e ? srcN : nullptr, fd, lv,
-                                                 tst, bacc_up, bacc_dn, coef, tabT);
+                                                 tst, bacc_up, bacc_dn, coef, tabT, ra);
                 wR = wF;
                 up = !up;
             }
             dispatch_pass<Real, MM, false, V>(lw, up, lane, nl, Lp, Real(0), wR, bs, bg, nullptr, s < s1 ? srcN : nullptr, fd, lv,
-                                              tst, bacc_up, bacc_dn, coef, tabT);
+                                              tst, bacc_up, bacc_dn, coef, tabT, ra);
             up = !up;
             // ---- partial band sums of this (warp, band) run -> scratch slot ---------------------------
             __syncwarp();
@@ -1415,6 +1576,21 @@ __global__ void __launch_bounds__(variant_threads(V), 1) flux_kernel(const FluxA
                     o[i] = su;
                     o[L + i] = sd;
                 }
+            } else if constexpr (RS) {
+                // group accumulators: indexed by layer; an upward layer k is interface k (padding layers >= nl
+                // hold junk), a downward layer k interface k + 1
+                for (int i = lane; i < L; i += 32) {
+                    double su = bacc_up[i], sd = bacc_dn[i];
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) {
+                        if (i < nl) su += b4[g * LS4 + i];
+                        if (i >= 1) sd += b4[(4 + g) * LS4 + i - 1];
+                    }
+                    o[i] = su;
+                    o[L + i] = sd;
+                }
+                __syncwarp();
+                for (int i = lane; i < 8 * LS4; i += 32) b4[i] = 0.0;
             } else {
                 for (int i = lane; i < L; i += 32) {
                     o[i] = bacc_up[i];

@@ -236,28 +236,36 @@ def test_whole_column_mode_equals_split_mode():
 
 @pytest.mark.parametrize('precision', ['f64', 'f32'])
 def test_tensor_memory_tstore_equals_shared_memory_tstore(precision, monkeypatch):
-    """The default kernel keeps the per-lane t-store in tensor memory (LDTM / STTM) and stages the
+    """CMB200_FLUX_VARIANT=3 keeps the per-lane t-store in tensor memory (LDTM / STTM) and stages the
     long-wave coefficient rows in shared memory; CMB200_FLUX_VARIANT=0 selects the plain kernel
     (t-store in shared memory, coefficients broadcast with shuffles).  Same arithmetic in the same
     order: the results are equal bit for bit, in both optical-depth sources, split and whole-column
-    mode."""
+    mode.  Variant 3 is the FP32 default; the FP64 default adds the shared-memory exp table (error
+    <= 1e-14 per layer) and the direct short-wave pass, and has to stay within 1e-12 of them."""
     c = load_case('two_mol_nz41')
     plan = make_plan(c, precision=precision, tables=True)
     tau = oracle_tau(c)
     for n_col in (3, 1300):
         T, T_g, T_tau, albedo, q = batch_inputs(c, n_col, seed=11)
         res = {}
-        for variant in ('0', None):
+        for variant in ('0', '3', None):
             if variant is None:
                 monkeypatch.delenv('CMB200_FLUX_VARIANT', raising=False)
             else:
                 monkeypatch.setenv('CMB200_FLUX_VARIANT', variant)
             res[variant] = (plan.flux(T, T_g, T_tau=T_tau, q=q, albedo=albedo),
                             plan.flux(T, T_g, tau=tau, albedo=albedo))
-        for a, b in zip(res['0'], res[None]):
+        for a, b, d in zip(res['0'], res['3'], res[None]):
             for k in ('up', 'down', 'net', 'heating'):
-                assert np.isfinite(b[k]).all()
+                assert np.isfinite(b[k]).all() and np.isfinite(d[k]).all()
                 assert np.array_equal(a[k], b[k])
+                if precision == 'f32':
+                    assert np.array_equal(a[k], d[k])
+                elif k != 'heating':
+                    assert relmax(d[k], a[k]) < 1e-12
+                else:
+                    for i in range(min(n_col, 16)):
+                        assert heating_ok(d[k][i], a[k][i], d['up'][i], d['down'][i], c['bands']['delta'], c['P'], 1e-10)
 
 
 def test_tau_id_selects_table():
