@@ -102,6 +102,7 @@ SIGNATURES = {
     'cmb200_launch_count': (C.c_int64, []),
     'cmb200_test_exp_neg_host': (C.c_int, [c_double_p, C.c_int64, c_double_p]),
     'cmb200_measure_peaks': (C.c_int, [C.c_int, c_double_p, c_double_p, c_double_p]),
+    'cmb200_measure_peaks2': (C.c_int, [C.c_int, c_double_p, c_double_p, c_double_p]),
 }
 
 
@@ -168,4 +169,7 @@ def launch_count():
 def measure_peaks(device=0):
     a, b, c = C.c_double(), C.c_double(), C.c_double()
     check(load().cmb200_measure_peaks(device, C.byref(a), C.byref(b), C.byref(c)))
-    return {'fp64_tflops': a.value, 'fp32_tflops': b.value, 'copy_gbs': c.value}
+    d, e, f = C.c_double(), C.c_double(), C.c_double()
+    check(load().cmb200_measure_peaks2(device, C.byref(d), C.byref(e), C.byref(f)))
+    return {'fp64_tflops': a.value, 'fp32_tflops': b.value, 'copy_gbs': c.value,
+            'fp64_reg_tflops': d.value, 'fp32_reg_tflops': e.value, 'l2_stream_gbs': f.value}

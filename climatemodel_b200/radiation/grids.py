@@ -2,8 +2,11 @@
 and the fixed-size pressure grid that ``RealGas.__init__`` derives before any flux is computed
 (real_gas.py:300-334 get_wavenumber_array, :336-402 get_wavenumber_bands, :493-503 the integer-nz
 branch of get_p_grid).  One-off O(n_nu) set-up work, NumPy on the host (SURVEY.md section 2,
-row 3); the Planck evaluations go through ``planck`` which defaults to the CUDA
-``B_wavenumber``.
+row 3).  The Planck values behind the band / grid edges are evaluated in host NumPy with exactly
+the reference's expression (``B_freq`` / ``B_wavenumber``, real_gas.py:14-42: ``freq ** 3``, the
+same operation order), because the edges are arg-min decisions: a last-bit difference of another
+Planck routine (the CUDA one cubes with two multiplications) could flip a near-tie and move an edge
+by one bin.  The CUDA Planck function stays on the hot path only.
 
 Results must match the reference *exactly* (band edges are argmin decisions), which the tests
 check against the golden cases.
@@ -13,9 +16,17 @@ from math import ceil
 import numpy as np
 
 
+def planck_wavenumber_host(nu, T):
+    """B(nu, T) per wavenumber (cm^-1), W m^-2 / cm^-1 -- the reference's B_wavenumber (real_gas.py:30-42)
+    on B_freq (:14-27) written out in NumPy, operation for operation."""
+    from ..constants import h_planck, speed_of_light, k_boltzmann
+    freq = 100 * np.asarray(nu, dtype=float) * speed_of_light
+    B = 2 * h_planck * freq ** 3 / speed_of_light ** 2 / (np.exp(h_planck * freq / (k_boltzmann * T)) - 1)
+    return 100 * speed_of_light * B
+
+
 def _default_planck():
-    from .real_gas import B_wavenumber
-    return B_wavenumber
+    return planck_wavenumber_host
 
 
 def fixed_pressure_grid(nz, p_surface, p_toa):

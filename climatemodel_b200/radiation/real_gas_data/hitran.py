@@ -23,12 +23,13 @@ _cache = {}
 
 def load_table(molecule_name, folder=None):
     """Return the table dict of ``molecule_name``.  Unlike the reference, which re-reads the file
-    on every ``load_absorption_coef`` call (real_gas.py:77), tables are cached per path+mtime."""
+    on every ``load_absorption_coef`` call (real_gas.py:77), tables are cached per path, mtime and size."""
     folder = LookupTableFolder if folder is None else folder
     for ext in ('.npy', '.npz'):
         path = os.path.join(folder, molecule_name + ext)
         if os.path.exists(path):
-            key = (path, os.path.getmtime(path))
+            st = os.stat(path)
+            key = (path, st.st_mtime_ns, st.st_size)
             if key not in _cache:
                 if ext == '.npy':
                     d = np.load(path, allow_pickle=True).item()
@@ -37,7 +38,10 @@ def load_table(molecule_name, folder=None):
                     d = {k: z[k] for k in z.files}
                 _cache[key] = {k: np.asarray(d[k]) for k in ('p', 'T', 'nu', 'absorption_coef')}
             return _cache[key]
-    raise FileNotFoundError('no lookup table %s(.npy|.npz) in %s' % (molecule_name, folder))
+    raise FileNotFoundError('no lookup table %s(.npy|.npz) in %s -- point hitran.LookupTableFolder (or the environment '
+                            'variable CLIMATEMODEL_LOOKUP_TABLES) at a folder of tables in the reference\'s format; the '
+                            'reference\'s three shipped tables are kept as test fixtures under tests/golden/tables'
+                            % (molecule_name, folder))
 
 
 # ---- building tables: line-by-line absorption coefficient (hitran.py:122-247, 315-356) -----------------

@@ -30,7 +30,7 @@ class RealGas(Atmosphere):
         the reference behaviour: ``precision`` ('f64' | 'f32' arithmetic of the wavenumber-resolved
         stage) and the CUDA ``device``."""
         self.precision, self.device = precision, device
-        self._plan, self._plan_key = None, None
+        self._plan, self._plan_no_emission, self._plan_key_seen, self._star_seen = None, None, None, None
         self.star = {'T': T_star, 'R': R_star, 'star_planet_dist': star_planet_dist}
         F_stellar_constant = sigma * T_star ** 4 * R_star ** 2 / star_planet_dist ** 2
         super().__init__(nz, ny, F_stellar_constant, albedo, p_surface, p_toa, temp_change, delta_temp_change)
@@ -138,41 +138,57 @@ class RealGas(Atmosphere):
         return np.tile(10 ** levels, (self.ny, 1)).transpose()
 
     # ---- the hot path ---------------------------------------------------------------------------------
-    def _flux_plan(self):
-        key = (id(self.nu), id(self.nu_bands), id(self.p_interface), self.nu.size, self.p_interface.shape[0])
-        if self._plan is None or key != self._plan_key:
-            if self._plan is not None:
-                self._plan.close()
-            self._plan = FluxPlan(self.p_interface[:, 0], self.nu, bands_from_nu_bands(self.nu, self.nu_bands),
-                                  precision=self.precision, device=self.device, T_star=self.star['T'],
-                                  R_star=self.star['R'], star_planet_dist=self.star['star_planet_dist'])
-            self._plan_key = key
-        return self._plan
+    def _plan_key(self):
+        """What a FluxPlan is built from: the grids (their bytes, not their identities -- callers may edit
+        bands or rebuild arrays in place) and the star (re-read on every evaluation, like the reference
+        reads self.star in get_flux, real_gas.py:640-642)."""
+        import hashlib
+        h = hashlib.blake2b(digest_size=16)
+        for a in (self.nu, self.p_interface, self.nu_bands['centre'], self.nu_bands['delta'], self.nu_bands['sw'],
+                  np.array([len(r) for r in self.nu_bands['range']]), np.array([r[0] for r in self.nu_bands['range']])):
+            h.update(np.ascontiguousarray(a).tobytes())
+        return h.hexdigest(), (float(self.star['T']), float(self.star['R']), float(self.star['star_planet_dist']))
 
-    def _evaluate(self, outputs):
+    def _make_plan(self, bands):
+        return FluxPlan(self.p_interface[:, 0], self.nu, bands, precision=self.precision, device=self.device,
+                        T_star=self.star['T'], R_star=self.star['R'], star_planet_dist=self.star['star_planet_dist'])
+
+    def _flux_plan(self, no_emission=False):
+        grids_key, star = self._plan_key()
+        if self._plan is None or grids_key != self._plan_key_seen:
+            for old in (self._plan, self._plan_no_emission):
+                if old is not None:
+                    old.close()
+            self._plan = self._make_plan(bands_from_nu_bands(self.nu, self.nu_bands))
+            self._plan_no_emission, self._plan_key_seen, self._star_seen = None, grids_key, star
+        if no_emission and self._plan_no_emission is None:
+            # every band treated as short-wave: the sweep without emission integrals (OLR breakdown)
+            bands = bands_from_nu_bands(self.nu, self.nu_bands)
+            bands['sw'] = np.ones_like(bands['sw'])
+            self._plan_no_emission = self._make_plan(bands)
+        if star != self._star_seen:
+            for plan in (self._plan, self._plan_no_emission):
+                if plan is not None:
+                    plan.set_star(*star)
+            self._star_seen = star
+        return self._plan_no_emission if no_emission else self._plan
+
+    def _evaluate(self, outputs, no_emission=False):
         albedo = float(np.ravel(self.albedo)[0])
-        return self._flux_plan().flux(np.asarray(self.T, dtype=float)[:, 0], float(np.ravel(self.T_g)[0]),
-                                      tau=self.tau_interface, albedo=albedo, outputs=outputs)
+        return self._flux_plan(no_emission).flux(np.asarray(self.T, dtype=float)[:, 0], float(np.ravel(self.T_g)[0]),
+                                                 tau=self.tau_interface, albedo=albedo, outputs=outputs)
 
     def get_flux(self, include_olr_breakdown=False):
         """(up_flux, down_flux), each [nz x n_nu_bands] in W m^-2 / cm^-1 (real_gas.py:629-669).
-        With include_olr_breakdown the contribution of every level to the top-of-atmosphere up
-        flux, olr_cont [nz x n_nu_bands], is returned as well: the surface row from the transmitted
-        surface emission, the others from differences of the emission integrals."""
+        With include_olr_breakdown the contributions to the top-of-atmosphere up flux are returned as well
+        (olr_cont: 'surface' = transmitted surface emission, 'atmos' = the emission integral, :643-667)."""
         out = self._evaluate(('up', 'down'))
         up, down = out['up'][0], out['down'][0]
         if not include_olr_breakdown:
             return up, down
-        # surface part = transmitted surface emission: the same sweep with every band treated as
-        # short-wave (no emission integrals); the atmosphere's part is the rest (real_gas.py:656-667)
-        bands = bands_from_nu_bands(self.nu, self.nu_bands)
-        bands['sw'] = np.ones_like(bands['sw'])
-        no_emission = FluxPlan(self.p_interface[:, 0], self.nu, bands, precision=self.precision, device=self.device,
-                               T_star=self.star['T'], R_star=self.star['R'],
-                               star_planet_dist=self.star['star_planet_dist'])
-        surf = no_emission.flux(np.asarray(self.T, dtype=float)[:, 0], float(np.ravel(self.T_g)[0]),
-                                tau=self.tau_interface, albedo=float(np.ravel(self.albedo)[0]), outputs=('up',))
-        no_emission.close()
+        # surface part = the same sweep with every band treated as short-wave (no emission integrals; the
+        # plan for it is built once and kept); the atmosphere's part is the rest (real_gas.py:656-667)
+        surf = self._evaluate(('up',), no_emission=True)
         surface = surf['up'][0][0].copy()
         atmos = np.where(self.nu_bands['sw'], 0.0, up[0] - surface)
         return up, down, {'surface': surface, 'atmos': atmos}

@@ -253,6 +253,11 @@ int cmb200_grey_flux_host(int32_t nz, int64_t ny, double sigma, const double *T,
 /* Issue-rate microbenchmarks on the plan-independent current device: dependent-chain-free
  * DFMA and FFMA loops (TFLOP/s, 2 flop per FMA) and a device copy (GB/s, read+write). */
 int cmb200_measure_peaks(int device, double *fp64_tflops, double *fp32_tflops, double *copy_gbs);
+/* Denominators measured the way the flux kernel runs (one CTA of 8 warps per SM): DFMA / FFMA loops
+ * whose multiplier and addend sit in registers (TFLOP/s), and the L2 -> SM read bandwidth -- a 64 MB
+ * L2-resident buffer read repeatedly with coalesced 16-byte loads at full occupancy (GB/s), the ceiling of
+ * the flux kernel's table stream.  Any pointer may be NULL. */
+int cmb200_measure_peaks2(int device, double *fp64_reg_tflops, double *fp32_reg_tflops, double *l2_stream_gbs);
 
 /* Test hook: the flux kernel's own exp(-x) routine evaluated on n values (HOST pointers). */
 int cmb200_test_exp_neg_host(const double *x, int64_t n, double *out);

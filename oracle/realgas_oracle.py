@@ -281,7 +281,15 @@ def get_flux(P, T, T_g, tau, nu, bands, T_star=T_sun, R_star=R_sun, dist=AU, alb
     dn = np.zeros((L, B))
     for j in range(B):
         c = bands['centre'][j]
-        Tr = band_transmission_matrix(tau, int(bands['start'][j]), int(bands['len'][j]), nu, bands['delta'][j])
+        s0, n0, dj = int(bands['start'][j]), int(bands['len'][j]), bands['delta'][j]
+        if bands['sw'][j]:
+            # short-wave band: the reference evaluates only Trans(i, L-1) and Trans(0, i) (:647-655),
+            # two length-L vectors, not the L x L matrix
+            t, x = tau[:, s0:s0 + n0], nu[s0:s0 + n0]
+            up[:, j] = np.pi * planck_wavenumber(c, T_g) * _trapz(np.exp(t - t[L - 1]), x, axis=1) / dj
+            dn[:, j] = np.pi * planck_wavenumber(c, T_star) * solar * _trapz(np.exp(t[0] - t), x, axis=1) / dj
+            continue
+        Tr = band_transmission_matrix(tau, s0, n0, nu, dj)
         up[:, j] = np.pi * planck_wavenumber(c, T_g) * Tr[:, L - 1]                 # :638, :647
         dn[:, j] = np.pi * planck_wavenumber(c, T_star) * solar * Tr[0, :]          # :640-642, :652
         if not bands['sw'][j]:

@@ -14,8 +14,10 @@ installed (no network):
 Both are replaced by stubs registered in ``sys.modules``.  ``np.trapz`` is
 aliased to ``np.trapezoid`` when a future NumPy drops it.
 
-``/root/reference`` exists only in the build container -- nothing that runs on
-the GPU box (``-m gpu`` tests, ``smoke()``, ``bench.py``) may import this file.
+``/root/reference`` exists only in the build container.  On the GPU box the shim
+falls back to the unmodified copy staged under ``oracle/_ref`` (oracle/make_ref.py):
+that is what ``bench.py --impl reference`` and the ``cpu_baseline`` leg time.  The
+``-m gpu`` tests and ``smoke()`` never import this file.
 """
 import importlib
 import os
@@ -25,7 +27,11 @@ import warnings
 
 import numpy as np
 
-REFERENCE_ROOT = os.environ.get("CLIMATEMODEL_REFERENCE_ROOT", "/root/reference")
+# The reference itself in the build container; on the GPU box (no /root/reference) the unmodified copy
+# that oracle/make_ref.py staged under oracle/_ref (git-ignored, travels with the snapshot).
+_STAGED = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+REFERENCE_ROOT = os.environ.get("CLIMATEMODEL_REFERENCE_ROOT") or (
+    "/root/reference" if os.path.isdir("/root/reference/Model/radiation") else _STAGED)
 
 # sympl 0.4.x default_constants values for the 12 names Model/constants.py:3-16 asks for.
 # Only reference_air_pressure is pinned by a reference artefact (CO2_no_sw.npy p.max()=101320);

@@ -132,15 +132,17 @@ def test_dtransmission_dq(rg):
 
 
 # ---- A6-A9: resident tau ----------------------------------------------------------------------
-def heating_ok(got, ref, up, dn, delta, P, tol):
+def heating_ok(got, ref, up, dn, delta, P, tol, eps=np.finfo(float).eps):
     """Heating rate = g/c_p d(net)/dp with net = sum_j up_j delta_j - sum_j dn_j delta_j: a
     difference of differences of nearly equal numbers, so even the reference's own FP64
     evaluation carries rounding noise of a few ulp of those band sums divided by dp.  Pass when
     the norm-wise error is below ``tol`` (north_star: 1e-10) or below that intrinsic floor,
-    16 eps max(sum_j up_j delta_j) g/c_p / dp per layer."""
+    16 eps max(sum_j up_j delta_j) g/c_p / dp per layer.  ``eps`` is the unit
+    roundoff of the arithmetic the wavenumber-resolved stage ran in: FP32 mode carries every chain in
+    single precision, so its floor is the FP32 analogue (the band sums themselves are added in FP64)."""
     err = np.abs(np.asarray(got) - ref)
     mag = max(np.sum(np.abs(up) * delta, axis=1).max(), np.sum(np.abs(dn) * delta, axis=1).max())
-    floor = 16 * np.finfo(float).eps * mag * orc.g / orc.c_p_dry / np.diff(P)
+    floor = 16 * eps * mag * orc.g / orc.c_p_dry / np.diff(P)
     return bool(np.all((err <= tol * np.abs(ref).max()) | (err <= floor)))
 
 
@@ -177,10 +179,17 @@ def test_flux_fp32_mode(name):
     assert relmax(out['up'][0], c['up']) < TOL32
     assert relmax(out['down'][0], c['down']) < TOL32
     assert relmax(out['net'][0], c['net']) < TOL32
+    eps32 = float(np.finfo(np.float32).eps)
+    assert heating_ok(out['heating'][0], c['heating'], c['up'], c['down'], c['band_delta'], c['P'], TOL32, eps=eps32)
     out = plan.flux(c['T'], c['T_g'], T_tau=c['T_interface_tau'], q=c['q'], albedo=c['albedo'])
     assert relmax(out['up'][0], c['up']) < TOL32
     assert relmax(out['down'][0], c['down']) < TOL32
     assert relmax(out['net'][0], c['net']) < TOL32
+    # heating rate (north_star: <= 1e-5 in FP32 mode): norm-wise, or below the FP32 rounding floor of the
+    # difference of band sums it is made of -- and never worse than a few FP32 ulp of the net flux per layer
+    assert heating_ok(out['heating'][0], c['heating'], c['up'], c['down'], c['band_delta'], c['P'], TOL32, eps=eps32)
+    dnet = np.abs(np.diff(out['net'][0]) - np.diff(c['net']))
+    assert dnet.max() <= 32 * eps32 * np.abs(c['net']).max()
 
 
 # ---- batched columns ------------------------------------------------------------------------------
