@@ -96,6 +96,8 @@ SIGNATURES = {
                                    c_int32_p, c_int32_p, C.POINTER(C.c_int64)]),
     'cmb200_plan_optical_depth': (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
                                             C.c_int, C.c_void_p, C.c_void_p]),
+    'cmb200_plan_optical_depth_noalloc': (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
+                                            C.c_int, C.c_void_p, C.c_void_p]),
     'cmb200_flux': (C.c_int, [C.c_void_p, C.POINTER(FluxIO), C.c_void_p]),
     'cmb200_flux_host': (C.c_int, [C.c_void_p, C.POINTER(FluxIO)]),
     'cmb200_flux_workspace_bytes': (C.c_int, [C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]),

@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 PKG = os.path.dirname(HERE)
 LIB = os.path.join(PKG, 'libclimatemodel_b200.so')
 SOURCES = ['unity.cu', 'plan.cu', 'tables.cu', 'flux.cu', 'transmission.cu', 'peaks.cu', 'lines.cu',
-           'convect.cu', 'stepper.cu', 'grey.cu', 'common.cuh', 'internal.cuh', 'flux_kernels.cuh', 'tmem.cuh',
+           'convect.cu', 'stepper.cu', 'grey.cu', 'noalloc.cu', 'common.cuh', 'internal.cuh', 'flux_kernels.cuh', 'tmem.cuh',
            os.path.join('..', '..', 'include', 'climatemodel_b200.h')]
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17',
               '--expt-relaxed-constexpr', '--expt-extended-lambda',

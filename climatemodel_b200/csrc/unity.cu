@@ -3,6 +3,7 @@
 #include "plan.cu"
 #include "tables.cu"
 #include "flux.cu"
+#include "noalloc.cu"
 #include "transmission.cu"
 #include "peaks.cu"
 #include "lines.cu"

@@ -381,3 +381,21 @@ class FluxPlan:
             T_g.data_ptr() if T_g is not None else None, q.data_ptr(), per_col, tau.data_ptr(),
             C.c_void_p(stream)))
         return tau
+
+    def optical_depth_noalloc(self, q, tau, T_tau=None, T_g=None):
+        """``optical_depth_device`` for callers that must not allocate (CUDA graph capture, serving loops):
+        the caller passes the output ``tau`` [n_col, L, N] (contiguous float64 CUDA tensor) and
+        cmb200_plan_optical_depth_noalloc fills it using a fixed 1 MiB device array as scratch, so
+        M * n_col * L <= 1,048,576 (ValueError beyond).  Calls that overlap on the GPU race on that
+        array.  No counterpart in the reference."""
+        import torch
+        n_col = tau.shape[0]
+        if tau.shape != (n_col, self.L, self.N) or tau.dtype != torch.float64 or not tau.is_contiguous():
+            raise ValueError('tau must be a contiguous float64 tensor [n_col, %d, %d]' % (self.L, self.N))
+        per_col = 1 if q.dim() == 3 else 0
+        stream = torch.cuda.current_stream(tau.device).cuda_stream
+        check(self._lib.cmb200_plan_optical_depth_noalloc(
+            self._h, n_col, T_tau.data_ptr() if T_tau is not None else None,
+            T_g.data_ptr() if T_g is not None else None, q.data_ptr(), per_col, tau.data_ptr(),
+            C.c_void_p(stream)))
+        return tau

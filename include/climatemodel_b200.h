@@ -149,6 +149,21 @@ int cmb200_plan_optical_depth(cmb200_plan *plan, int64_t n_col, const double *T_
                               const double *T_g, const double *q, int q_per_column,
                               double *tau, void *stream);
 
+/* cmb200_plan_optical_depth without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same arguments, same arithmetic, same results as
+ * cmb200_plan_optical_depth; the one scratch buffer of that call (the table-temperature row index per
+ * molecule, column and level) lives in a file-scope device array of 1 MiB that every GPU loading the
+ * library holds until exit, so plan M x n_col x L must be <= 1,048,576 (CMB200_ERR_ARG with a message
+ * otherwise; n_col <= 65535 as for the regular call).  Calls no cudaMalloc / cudaFree / allocating
+ * library routine; the first call on a device looks the array's address up (cudaGetSymbolAddress).
+ * All calls on a device share the array, which keeps the last call's contents (every entry a call reads
+ * is rewritten by that call first, so nothing needs clearing): calls whose kernels overlap on the GPU
+ * race -- keep them on one stream or order them with events. */
+int cmb200_plan_optical_depth_noalloc(cmb200_plan *plan, int64_t n_col, const double *T_tau,
+                                      const double *T_g, const double *q, int q_per_column,
+                                      double *tau, void *stream);
+
 /* ---- A6-A9  fluxes, net flux, heating rate -------------------------------------------------- */
 typedef struct {
     int64_t n_col;
