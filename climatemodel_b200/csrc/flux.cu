@@ -41,7 +41,22 @@ static double cost_knob(const char *name, double dflt) {
 // Work decomposition: W warps per CTA (from the shared-memory budget), C CTAs per column (more
 // than one only when there are fewer columns than resident CTAs), parts = C * W contiguous runs
 // of segments of equal estimated cost, and one partial-sum slot per (part, band) run.
-static int ensure_partition(cmb200_plan *p, int64_t n_col, int W, int resident_ctas) {
+// Pass costs in units of one short-wave fresh pass, fitted to per-warp cycle counts (CMB200_DEBUG_TIMING) of the
+// kernel family: a long-wave fresh pass, and what a (part, band) run adds at its end (replay-only pass, write-out
+// of the partial sums) for short- and long-wave bands.  Model 1 = direct short-wave passes with the tensor-memory
+// lane sum (their short-wave pass is cheaper, so everything else weighs more), model 0 = the other kernels.
+struct PassCosts {
+    double lw, run_sw, run_lw;
+};
+static PassCosts pass_costs(int model) {
+    PassCosts c = model == 1 ? PassCosts{1.7, 0.65, 0.7} : PassCosts{1.5, 0.4, 0.6};
+    c.lw = cost_knob("CMB200_COST_LW", c.lw);
+    c.run_sw = cost_knob("CMB200_COST_RUN_SW", c.run_sw);
+    c.run_lw = cost_knob("CMB200_COST_RUN_LW", c.run_lw);
+    return c;
+}
+
+static int ensure_partition(cmb200_plan *p, int64_t n_col, int W, int resident_ctas, int cost_model) {
     Partition &pt = p->partition;
     // CTAs per column: with few columns a column is split over C CTAs so that the n_col * C tasks fill
     // the resident CTAs in whole waves -- pick the C with the least (waves / C), a little bias to small C.
@@ -59,14 +74,14 @@ static int ensure_partition(cmb200_plan *p, int64_t n_col, int W, int resident_c
             }
         }
     }
-    if (pt.n_col >= 0 && pt.warps == W && pt.ctas_per_col == C) return CMB200_OK;   // same decomposition
+    if (pt.n_col >= 0 && pt.warps == W && pt.ctas_per_col == C && pt.cost_model == cost_model) return CMB200_OK;   // same decomposition
     const int parts = C * W, n_seg = p->n_seg;
-    const double kCostLW = cost_knob("CMB200_COST_LW", 1.5), kCostRun = cost_knob("CMB200_COST_RUN", 0.4);
+    const PassCosts pc = pass_costs(cost_model);
     std::vector<double> prefix(n_seg + 1, 0.0);
     for (int s = 0; s < n_seg; ++s) {
         const int j = p->hseg_band[s];
-        double c = p->hsw[j] ? 1.0 : kCostLW;
-        if (s == 0 || p->hseg_band[s - 1] != j) c += kCostRun * (p->hsw[j] ? 1.0 : kCostLW);
+        double c = p->hsw[j] ? 1.0 : pc.lw;
+        if (s == 0 || p->hseg_band[s - 1] != j) c += p->hsw[j] ? pc.run_sw : pc.run_lw;
         prefix[s + 1] = prefix[s] + c;
     }
     std::vector<int32_t> seg0(parts + 1), slot0(parts), bslot(p->B + 1, 0);
@@ -91,6 +106,7 @@ static int ensure_partition(cmb200_plan *p, int64_t n_col, int W, int resident_c
     for (int j = 0; j <= p->B; ++j)
         bslot[j] = (int32_t)(std::lower_bound(slot_band.begin(), slot_band.end(), j) - slot_band.begin());
     pt.warps = W;
+    pt.cost_model = cost_model;
     pt.ctas_per_col = C;
     pt.parts = parts;
     pt.n_slots = (int)slot_band.size();
@@ -128,6 +144,7 @@ static int variant_warps(int L, int max_smem, int *tmem_cpw, int *tmem_cols, int
         const int cpw = *tm_rows * wpr;
         int cols = 32;
         while (cols < per_quarter * cpw) cols *= 2;
+        if ((V & kVarRedTmem) && cols < 512 && cols < per_quarter * (cpw + 2 * kU)) cols *= 2;   // exchange columns
         *tmem_cpw = cpw;
         *tmem_cols = cols;
     }
@@ -151,10 +168,14 @@ constexpr int kReferenceVariant = kVarTmem | kVarCoefSmem;
 template <typename Real, int MM>
 constexpr int default_variant() {
     if (!std::is_same<Real, double>::value) return kReferenceVariant;
-    return MM > 0 ? (kReferenceVariant | kVarExpLds | kVarSwDirect) : (kReferenceVariant | kVarExpLds);
+    return MM > 0 ? (kReferenceVariant | kVarExpLds | kVarSwDirect | kVarRedTmem | kVarSmallSt) : (kReferenceVariant | kVarExpLds);
 }
 #ifndef CMB_FLUX_EXPERIMENTS
+#ifdef CMB_DEV_BUILD
 #define CMB_FLUX_EXPERIMENTS(X)
+#else
+#define CMB_FLUX_EXPERIMENTS(X)
+#endif
 #endif
 static int flux_variant() {          // -1: the default of the (type, source) at hand
     const char *e = getenv("CMB200_FLUX_VARIANT");
@@ -205,7 +226,7 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
         int c0, c1, c2;
         if (W < variant_warps<Real, MM, 0>(L, max_smem, &c0, &c1, &c2)) return launch_flux<Real, MM, 0>(p, io, Tint, s);
     }
-    const CtaSmem<Real, MM, V> lay(L, (V & kVarMixed) ? Lp - tm_rows : -1);
+    const CtaSmem<Real, MM, V> lay(L, (V & kVarMixed) ? Lp - tm_rows : -1, p->B);
     if (W < 1) {
         set_error("%d levels need %zu bytes of shared memory per CTA; the device offers %d", L, lay.total(1), max_smem);
         return CMB200_ERR_LIMIT;
@@ -214,21 +235,24 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     // columns): ask for more than half of the shared memory.
     size_t smem = (V & kVarTmem) ? std::max(lay.total(W), (size_t)max_smem / 2 + 1024) : lay.total(W);
     if constexpr ((V & kVarSwDirect) != 0) {
-        // the exp table occupies shared-window addresses [0x10000, 0x20000): everything else has to end below
-        // 0x10000 (the window starts at a small driver-reserved offset), and the window has to reach 0x20000
-        if (lay.total(W) + 2048 > kXlWindow || (size_t)max_smem < 2 * (size_t)kXlWindow)
-            return launch_flux<Real, MM, V & ~(kVarSwDirect | kVarRedSmem)>(p, io, Tint, s);
-        smem = 2 * (size_t)kXlWindow;
-        if constexpr ((V & kVarRedSmem) != 0) {      // group accumulators and exchange scratch of every warp above the table
-            smem += (size_t)W * red_warp_bytes(Lp);
-            if (smem > (size_t)max_smem) return launch_flux<Real, MM, V & ~kVarRedSmem>(p, io, Tint, s);
+        // the exp table occupies shared-window addresses [xl_window, xl_window + 64 kB): the level tables and the
+        // warps' regions have to end below it (the window starts at a small driver-reserved offset)
+        constexpr unsigned win = xl_window(V);
+        if (lay.total(W) + 2048 > win || (size_t)max_smem < (size_t)win + kXlBytes)
+            return launch_flux<Real, MM, V & ~(kVarSwDirect | kVarRedTmem | kVarSmallSt)>(p, io, Tint, s);
+        smem = (size_t)win + kXlBytes;
+        if constexpr ((V & kVarRedTmem) != 0) {
+            // the warps' coefficient rows sit above the table; the exchange columns follow the t-stores in tensor memory
+            smem += (size_t)W * lay.coef_bytes;
+            if (smem + 1024 > (size_t)max_smem || (W / 4) * (tmem_cpw + 2 * kU) > tmem_cols)
+                return launch_flux<Real, MM, V & ~(kVarRedTmem | kVarSmallSt)>(p, io, Tint, s);
         }
     }
     CMB_CUDA(cudaFuncSetAttribute(flux_kernel<Real, MM, V>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int ctas_per_sm = 1;
     CMB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, flux_kernel<Real, MM, V>, W * 32, smem));
     const int resident = sm_count(p->device) * std::max(1, ctas_per_sm);
-    int rc = ensure_partition(p, io->n_col, W, resident);
+    int rc = ensure_partition(p, io->n_col, W, resident, (V & kVarRedTmem) ? 1 : 0);
     if (rc) return rc;
     const Partition &pt = p->partition;
     if (pt.n_slots == 0) {     // no segment in this plan's band / segment range: every sum is empty
@@ -386,6 +410,10 @@ static int launch_flux_variant(int variant, cmb200_plan *plan, const cmb200_flux
     }
     if (variant == 0) return launch_flux<Real, MM, 0>(plan, io, Tint, s);
     if (variant == kReferenceVariant) return launch_flux<Real, MM, kReferenceVariant>(plan, io, Tint, s);
+    // the default's own fall-back (shuffle reduction instead of the tensor-memory transpose) is compiled anyway: A/B
+    if constexpr ((default_variant<Real, MM>() & kVarRedTmem) != 0)
+        if (variant == (default_variant<Real, MM>() & ~(kVarRedTmem | kVarSmallSt)))
+            return launch_flux<Real, MM, default_variant<Real, MM>() & ~(kVarRedTmem | kVarSmallSt)>(plan, io, Tint, s);
     return launch_flux<Real, MM, default_variant<Real, MM>()>(plan, io, Tint, s);
 }
 

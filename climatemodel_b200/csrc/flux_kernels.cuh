@@ -96,33 +96,36 @@ constexpr int kVarTmem = 1, kVarCoefSmem = 2, kVarPartial = 4, kVarMixed = 8, kV
 //                 iteration (stage 1, exp, both recurrences, t-store traffic), only the block's warp reduction
 //                 is carried into the next iteration; implies the shared-memory exp table at shared address
 //                 0x10000 (the CTA asks for 128 kB of dynamic shared memory).
-//   kVarRedSmem   (with kVarSwDirect) the warp reduction of a block's eight values goes through shared memory
-//                 instead of 18 shuffles + 28 selects: every lane parks its eight values in its row of a
-//                 per-warp scratch (4 STS.128), lane (g, c) = (lane >> 3, lane & 7) adds the values of layer c
-//                 from the eight rows of lane group g (8 conflict-free LDS.64) and keeps the result in ITS OWN
-//                 band accumulator b4[g][layer] -- the four group accumulators are added when the (warp, band)
-//                 run is written out.  Short-wave replay-only passes take the same route (sw_replay_pass).
-//   kVarSwPoly    (with kVarSwDirect) sw_fresh_pass evaluates exp with the degree-11 polynomial (15 FP64
-//                 instructions, no shared-memory lookup) instead of the table routine.
-constexpr int kVarExpLds = 1024, kVarTmPairs = 2048, kVarSwDirect = 4096, kVarRedSmem = 8192, kVarSwPoly = 16384;
-constexpr int kRedStride = 18;                              // doubles per scratch row (144 B: 16-byte slots rotate over the banks)
-// Group accumulators of kVarRedSmem: [2 directions][4 lane groups][LS4] doubles, LS4 * 8 = 64 (mod 128) so
-// that the two groups of a half-warp fall into different banks.
-__host__ __device__ inline int red_ls4(int Lp) { return (Lp % 16 == 8) ? Lp : Lp + 8; }
-__host__ __device__ inline size_t red_warp_bytes(int Lp) { return (size_t)2 * 4 * red_ls4(Lp) * 8 + (size_t)32 * kRedStride * 8; }
+//   kVarRedTmem   (with kVarSwDirect) the lane sum of a block's eight values goes through tensor memory instead of
+//                 18 shuffles + 28 selects: every lane parks its eight values in 16 exchange columns of its own
+//                 TMEM lane (one STTM.32x32b.x16), and two LDTM.16x256b.x2 hand thread (u, c) = (lane & 3, lane >> 2)
+//                 the values of layers u and u + 4 from lanes c, c + 8, c + 16, c + 24 -- a transpose done by the
+//                 access shapes, no shuffle.  The thread adds its four lanes and accumulates the two sums in ITS OWN
+//                 class accumulator pacc[block][u][c] (one LDS.128 / STS.128); the eight classes are added when the
+//                 (warp, band) run is written out.  Short-wave replay-only passes take the same route (sw_replay_pass).
+//   kVarSmallSt   (with kVarSwDirect) the direct short-wave passes store their blocks to tensor memory with eight
+//                 STTM.x2 (the register pair of each value) instead of one STTM.x16.
+constexpr int kVarExpLds = 1024, kVarTmPairs = 2048, kVarSwDirect = 4096, kVarRedTmem = 8192, kVarSmallSt = 16384;
+// Class accumulators of kVarRedTmem: [2 directions][Lp / kU blocks][32 lanes] double2 (x: layer u, y: layer u + 4 of the
+// block, u = lane & 3; class c = lane >> 2): every thread owns slot `lane` of every block, so a warp's LDS.128 /
+// STS.128 covers 512 contiguous bytes in lane order (no bank conflicts).
+__host__ __device__ inline size_t red_warp_bytes(int Lp) { return (size_t)2 * Lp * 8 * sizeof(double); }
 struct RedAux {
-    double *up_lane, *dn_lane;      // this lane's slot of the group accumulators at layer 0: b4[dir][g] + c
-    double *st_row;                 // scratch row of this lane
-    const double *ld_col;           // scratch element (first row of this lane's group, column c)
+    uint32_t scratch;               // tensor-memory address of this warp's 16 exchange columns (first lane of its quarter)
+    unsigned up, dn;                // shared-window address of this thread's slot of block 0 of the class accumulators, per direction
 };
-constexpr unsigned kXlWindow = 0x10000u;                    // kVarSwDirect: shared-window address of the exp table
+// kVarSwDirect: shared-window address of the exp table (64 kB, 64 kB aligned so that its entry address is one LOP3).
+// With kVarRedTmem the class accumulators need the room below it, so it moves up and the staged coefficient rows
+// of the warps go above it.
+constexpr unsigned xl_window(int V) { return (V & 8192) ? 0x20000u : 0x10000u; }
+constexpr unsigned kXlBytes = 0x10000u;
 constexpr int kXlN = 512, kXlLog = 9, kXlCopies = 16;       // table entries, log2, replicas
 // Per-warp handles of the exp tables: this lane's entry of the 2^(j/32) register table (kVarExpTable) and
 // the shared-memory table already offset by lane & 15 (kVarExpLds).
 struct ExpAux {
     double tabT;
     const double *lds;
-    unsigned saddr;       // kVarSwDirect: kXlWindow | (lane & 15) * 8
+    unsigned saddr;       // kVarSwDirect: xl_window(V) | (lane & 15) * 8
 };
 // Ablation switches for timing experiments only (results are wrong): skip the table loads after the
 // first block, the exp polynomial, the warp reduction, the t-store traffic.
@@ -187,11 +190,11 @@ __host__ __device__ inline int padded_layers(int L) { return ((L - 1) + kU - 1) 
 // once, then per warp the band accumulators and the t-store.
 template <typename Real, int MM, int V = 0>
 struct CtaSmem {
-    size_t off_offdn, off_offup, off_qg, off_hdp, shared_total, warp_bacc, warp_coef, warp_ts, warp_total;
+    size_t off_offdn, off_offup, off_qg, off_hdp, shared_total, warp_bacc, warp_coef, warp_pacc, coef_bytes, warp_ts, warp_total;
     int lev_stride;
     // ts_rows: layers of the t-store a warp keeps in shared memory (-1: all of them, or none with kVarTmem)
-    size_t off_xtab;
-    __host__ __device__ CtaSmem(int L, int ts_rows = -1) {
+    size_t off_xtab, off_bsrc;      // off_bsrc: [2][B] boundary sources of the column's bands (kVarRedTmem)
+    __host__ __device__ CtaSmem(int L, int ts_rows = -1, int B = 0) {
         auto up16 = [](size_t x) { return (x + 15) & ~(size_t)15; };
         const int Lp = padded_layers(L), MR = MM > 0 ? MM : 1;
         if (ts_rows < 0) ts_rows = (V & kVarTmem) ? 0 : Lp;
@@ -207,13 +210,22 @@ struct CtaSmem {
         b = up16(b + (size_t)Lp * sizeof(Real));
         off_xtab = b;
         if ((V & kVarExpLds) && !(V & kVarSwDirect)) b = up16(b + (size_t)kXlN * kXlCopies * sizeof(double));
+        off_bsrc = b;
+        if (V & kVarRedTmem) b = up16(b + (size_t)2 * B * sizeof(double));
         shared_total = b;
         // per warp: band accumulators (bacc_up, bacc_dn [Lp + kU] each, or the partial-sum layout
         // [2][Lp / 2][kPartialLanes][2]), the staged coefficient rows [4][Lp], the t-store [Lp][32]
         warp_bacc = 0;
         warp_coef = up16((V & kVarPartial) ? (size_t)2 * Lp * kPartialLanes * sizeof(double)
                                            : (size_t)2 * (Lp + kU) * sizeof(double));
-        warp_ts = up16(warp_coef + ((V & kVarCoefSmem) ? (size_t)4 * Lp * sizeof(Real) : 0));
+        coef_bytes = (V & kVarCoefSmem) ? (size_t)4 * Lp * sizeof(Real) : 0;
+        if (V & kVarRedTmem) {      // class accumulators here, coefficient rows above the exp table
+            warp_pacc = warp_coef;
+            warp_ts = up16(warp_pacc + red_warp_bytes(Lp));
+        } else {
+            warp_pacc = 0;
+            warp_ts = up16(warp_coef + coef_bytes);
+        }
         warp_total = up16(warp_ts + (size_t)ts_rows * 32 * sizeof(Real));
     }
     __host__ __device__ size_t total(int warps) const { return shared_total + warp_total * warps; }
@@ -997,58 +1009,100 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
     }
 }
 
-// kVarRedSmem: park the block's values, then fetch the eight partials this lane adds (row offsets are
-// compile-time).  Rows of group g = 2 g1 + g0: 8 (2 g1 + a) + 4 g0 + b, a < 2, b < 4 -- the two groups of a
-// half-warp read rows 4 apart, i.e. 64 bytes apart modulo the 128-byte bank row.
-__device__ __forceinline__ void red_exchange(const double (&v)[kU], const RedAux &ra, double (&part)[kU]) {
-    __syncwarp();                                   // everyone has read the previous block's rows
+// kVarRedTmem: the lane sum of a block's eight values through tensor memory (see the variant list).
+//   red_park   every lane writes its eight values to the warp's 16 exchange columns;
+//   red_fetch  (after the stores have landed) thread (u, c) = (lane & 3, lane >> 2) reads values u and u + 4 of
+//              lanes c, c + 8 (q0) and c + 16, c + 24 (q1); valid after the next tcgen05.wait::ld;
+//   red_accumulate  adds them, lanes in ascending order pairwise, to the thread's class accumulator.
+// A block of kU FP64 values -> 2 kU consecutive columns of the lane: one STTM.x16, or (SMALL) eight STTM.x2 whose
+// operand is the register pair the value was produced in -- ptxas assembles wider operand groups with moves
+// (two per value), a pair never needs one.
+template <bool SMALL>
+__device__ __forceinline__ void tm_store_block(uint32_t addr, const double (&v)[kU]) {
+    if constexpr (SMALL) {
 #pragma unroll
-    for (int i = 0; i < kU / 2; ++i) reinterpret_cast<double2 *>(ra.st_row)[i] = make_double2(v[2 * i], v[2 * i + 1]);
-    __syncwarp();
-#pragma unroll
-    for (int j = 0; j < kU; ++j) part[j] = ra.ld_col[(8 * (j >> 2) + (j & 3)) * kRedStride];
+        for (int u = 0; u < kU; ++u) {
+            uint32_t q[2] = {(uint32_t)__double2loint(v[u]), (uint32_t)__double2hiint(v[u])};
+            tmem::st_small<2>(addr + (uint32_t)(2 * u), q);
+        }
+    } else {
+        uint32_t w[2 * kU];
+        tmem::pack<kU>(v, w);
+        tmem::st<2 * kU>(addr, w);
+    }
 }
-__device__ __forceinline__ void red_accumulate(const double (&part)[kU], double *slot) {
-    const double s = ((part[0] + part[1]) + (part[2] + part[3])) + ((part[4] + part[5]) + (part[6] + part[7]));
-    *slot += s;
+template <bool SMALL>
+__device__ __forceinline__ void red_park(const double (&v)[kU], uint32_t scratch) {
+    tm_store_block<SMALL>(scratch, v);
+}
+__device__ __forceinline__ void red_fetch(uint32_t scratch, uint32_t (&q0)[8], uint32_t (&q1)[8]) {
+    tmem::wait_st();
+    tmem::ld_16x256b_x2(scratch, q0);
+    tmem::ld_16x256b_x2(scratch + (16u << 16), q1);
+}
+// (one 128-bit access each way, written as PTX: left to itself nvcc splits the pair into two 64-bit accesses
+// whose 16-byte lane stride costs two extra wavefronts)
+__device__ __forceinline__ double2 red_slot_load(unsigned slot) {
+    double2 a;
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(a.x), "=d"(a.y) : "r"(slot));
+    return a;
+}
+__device__ __forceinline__ void red_accumulate(const uint32_t (&q0)[8], const uint32_t (&q1)[8], double2 acc, unsigned slot) {
+    auto d = [](const uint32_t(&q)[8], int i) { return __hiloint2double((int)q[2 * i + 1], (int)q[2 * i]); };
+    acc.x += (d(q0, 0) + d(q0, 1)) + (d(q1, 0) + d(q1, 1));
+    acc.y += (d(q0, 2) + d(q0, 3)) + (d(q1, 2) + d(q1, 3));
+    asm volatile("st.shared.v2.f64 [%0], {%1, %2};" ::"r"(slot), "d"(acc.x), "d"(acc.y) : "memory");
 }
 
 // Replay-only pass of a short-wave band run (the last segment's chain in the direction it has not been swept
-// in yet): ER *= t read back from the t-store, values reduced through shared memory like sw_fresh_pass.
-template <bool UP>
+// in yet), in two phases.  Sweep: ER *= t read back from the t-store, and the value of every layer goes straight
+// back into the t-store columns its t came from (nobody needs that t again; the next run's first pass replays
+// with weight 0 and only wants finite numbers there).  Lane sums: the whole t-store is then read back with the
+// transposing loads, block after block with nothing serial between them, into the class accumulators.
+template <bool UP, bool SMALL>
 __device__ __forceinline__ void sw_replay_pass(const int Lp, const double wR, const double b0, const TStore<double> tst,
                                                const RedAux ra) {
     constexpr int NW = 2 * kU;
-    const int kfirst = UP ? Lp - kU : 0, kstep = UP ? -kU : kU;
+    const int kfirst = UP ? Lp - kU : 0, kstep = UP ? -kU : kU, nb = Lp / kU;
     double ER = wR * b0;
-    double part[kU];
-#pragma unroll
-    for (int u = 0; u < kU; ++u) part[u] = 0.0;
-    double *slot = UP ? ra.up_lane : ra.dn_lane;    // the first accumulate adds zeros to layer 0 + c
     uint32_t tw[NW];
     tmem::ld<NW>(tst.taddr + (uint32_t)(kfirst * 2), tw);
-    for (int it = 0, k0 = kfirst; it < Lp / kU; ++it, k0 += kstep) {
+    for (int it = 0, k0 = kfirst; it < nb; ++it, k0 += kstep) {
         double tR[kU], v[kU];
         tmem::wait_ld<NW>(tw);
         tmem::unpack<kU>(tw, tR);
-        if (it + 1 < Lp / kU) tmem::ld<NW>(tst.taddr + (uint32_t)((k0 + kstep) * 2), tw);
-        red_accumulate(part, slot);
+        if (it + 1 < nb) tmem::ld<NW>(tst.taddr + (uint32_t)((k0 + kstep) * 2), tw);
 #pragma unroll
         for (int o = 0; o < kU; ++o) {
             const int u = UP ? kU - 1 - o : o;
             ER *= tR[u];
             v[u] = ER;
         }
-        red_exchange(v, ra, part);
-        slot = (UP ? ra.up_lane : ra.dn_lane) + k0;
+        tm_store_block<SMALL>(tst.taddr + (uint32_t)(k0 * 2), v);
     }
-    red_accumulate(part, slot);
+    tmem::wait_st();
+    const unsigned base = UP ? ra.up : ra.dn;
+    uint32_t q0[8], q1[8];
+    tmem::ld_16x256b_x2(tst.taddr, q0);
+    tmem::ld_16x256b_x2(tst.taddr + (16u << 16), q1);
+    for (int b = 0; b < nb; ++b) {
+        uint32_t p0[8], p1[8];
+        const double2 acc = red_slot_load(base + b * 512);
+        tmem::wait_ld_pair(q0, q1);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) p0[i] = q0[i], p1[i] = q1[i];
+        if (b + 1 < nb) {
+            tmem::ld_16x256b_x2(tst.taddr + (uint32_t)((b + 1) * 2 * kU), q0);
+            tmem::ld_16x256b_x2(tst.taddr + (uint32_t)((b + 1) * 2 * kU) + (16u << 16), q1);
+        }
+        red_accumulate(p0, p1, acc, base + b * 512);
+    }
 }
 
 // ---- short-wave fresh pass, direct form (kVarSwDirect) -----------------------------------------------
 // Integer helpers written as PTX so that ptxas keeps them on the ALU pipe in the shape intended.
 __device__ __forceinline__ double xl_lookup(int n, unsigned saddr_lane) {
-    // entry j = n & 511 of the replicated table: byte offset j * 128 inside the 64 kB window at 0x10000
+    // entry j = n & 511 of the replicated table: byte offset j * 128 inside the 64 kB window the table fills
     unsigned s, a;
     asm("shf.l.wrap.b32 %0, %1, %1, 7;" : "=r"(s) : "r"(n));
     asm("lop3.b32 %0, %1, 0xff80, %2, 0xEA;" : "=r"(a) : "r"(s), "r"(saddr_lane));      // (s & 0xff80) | saddr_lane
@@ -1070,25 +1124,58 @@ __device__ __forceinline__ double xl_scale(double tt, int n) {
 // accumulators), but a block of kU layers is finished inside its iteration:
 //   table values of the block (loaded one block ahead) -> layer integrands -> thicknesses -> exp ->
 //   both recurrences -> park t;  then the next block's loads go out into the same registers.
-// Only the warp reduction of the block's eight values is carried: it is interleaved with the next block's
-// exp (its five shuffle stages are a ~160-cycle dependent chain).
+// Only the lane sum of the block's eight values is carried into the next iteration: five shuffle stages
+// interleaved with the next block's exp, or (kVarRedTmem) the transpose through tensor memory whose loads are
+// issued next to the replay chain's and complete behind the exp.
+// The table factor 2^(j/512) gets the 2^n of the result added to its exponent field BEFORE the last FMA, so
+// that FMA writes t straight into the register pair the t-store block and the recurrences read.
+// Level data by byte offset from the CTA's dynamic shared array: the address space is then known at every load
+// (LDS with the array's link-time base as immediate); through the generic pointers of LevelView the compiler
+// rebuilds the shared window base (S2UR of the CTA id + shifts) in front of every group of loads.
+extern __shared__ __align__(16) unsigned char smem_raw[];
+__device__ __forceinline__ void lds_f64x8(unsigned off, double (&o)[kU]) {
+#pragma unroll
+    for (int i = 0; i < kU / 2; ++i) {
+        const double2 q = *reinterpret_cast<const double2 *>(smem_raw + off + 16u * i);
+        o[2 * i] = q.x, o[2 * i + 1] = q.y;
+    }
+}
+__device__ __forceinline__ void lds_f64x8_m1(unsigned off, double (&o)[kU]) {      // off + 8 is 16-byte aligned
+    o[0] = *reinterpret_cast<const double *>(smem_raw + off);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        const double2 q = *reinterpret_cast<const double2 *>(smem_raw + off + 8u + 16u * i);
+        o[1 + 2 * i] = q.x, o[2 + 2 * i] = q.y;
+    }
+    o[7] = *reinterpret_cast<const double *>(smem_raw + off + 56u);
+}
+__device__ __forceinline__ void lds_u32x8(unsigned off, unsigned (&o)[kU]) {
+#pragma unroll
+    for (int i = 0; i < kU / 4; ++i) {
+        const uint4 q = *reinterpret_cast<const uint4 *>(smem_raw + off + 16u * i);
+        o[4 * i] = q.x, o[4 * i + 1] = q.y, o[4 * i + 2] = q.z, o[4 * i + 3] = q.w;
+    }
+}
+
 template <int MM, bool UP, int V>
 __device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, const int Lp, const double wF, const double wR,
                                               const double b0, const void *src_lane, const void *next_src,
                                               PassFeed<double, MM> &fd, const LevelView<double> lv,
                                               const TStore<double> tst, double *bacc, const ExpAux xaux, const RedAux ra) {
     static_assert(MM > 0, "table-fused path");
-    constexpr bool RS = (V & kVarRedSmem) != 0;
+    constexpr bool RT = (V & kVarRedTmem) != 0, SMALL = (V & kVarSmallSt) != 0;
     constexpr int NW = 2 * kU;
     constexpr double kK = 0x1.71547652b82fep+9, kMagic = 6755399441055744.0, kC = -0x1.62e42fefa39efp-10;
     const unsigned full = 0xffffffffu;
     const bool h4 = lane & 16, h3 = lane & 8, h2 = lane & 4;
     const int ridx = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
     const bool rlane = (lane & 3) == 0;
-    const int kfirst = UP ? Lp - kU : 0, kstep = UP ? -kU : kU;
+    const int kfirst = UP ? Lp - kU : 0, kstep = UP ? -kU : kU, nb = Lp / kU;
     const char *src_bytes = (const char *)src_lane;
-    const unsigned *offs = UP ? lv.off_up : lv.off_dn;
-    auto &raw = fd.raw;
+    // byte offsets of the level tables in the shared array: row offsets of this direction, q/g, half thicknesses
+    const unsigned s0 = (unsigned)__cvta_generic_to_shared(smem_raw);
+    const unsigned s_offs = (unsigned)__cvta_generic_to_shared(UP ? lv.off_up : lv.off_dn) - s0;
+    const unsigned s_qg = (unsigned)__cvta_generic_to_shared(lv.qg) - s0, s_hdp = (unsigned)__cvta_generic_to_shared(lv.hdp) - s0;
 
     double EF = wF * b0, ER = wR * b0;
     double Ic = 0.0;
@@ -1099,13 +1186,16 @@ __device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, cons
 #pragma unroll
     for (int u = 0; u < kU; ++u) v[u] = 0.0;
     int kprev = -kU * 4;        // block whose values v holds (none yet: its accumulate is predicated off)
-    double part[kU];            // kVarRedSmem: the eight partials of the previous block, and where their sum goes
-#pragma unroll
-    for (int u = 0; u < kU; ++u) part[u] = 0.0;
-    double *slot = UP ? ra.up_lane : ra.dn_lane;
+    // kVarRedTmem: class accumulator the pending lane sums go to; the first accumulate adds the zeros parked here
+    const unsigned cbase = UP ? ra.up : ra.dn;
+    unsigned slot = cbase + kfirst * 64;
+    if constexpr (RT) red_park<SMALL>(v, ra.scratch);
 
-    for (int it = 0, k0 = kfirst; it < Lp / kU; ++it, k0 += kstep) {
-        const bool last = it == Lp / kU - 1;
+    // (Tried and dropped: a second buffer of table values, i.e. loads issued two blocks ahead, the loop unrolled by
+    // two -- 9 % slower, profiles/r02_flux_variants_ab.json.  nvcc 12.9 note: the same body written as a lambda
+    // taking the buffer by reference came back with its arithmetic folded to NaN.)
+    for (int it = 0, k0 = kfirst; it < nb; ++it, k0 += kstep) {
+        auto &raw = fd.raw;
         // replay chain's t of this block
         uint32_t tRw[NW];
         if constexpr ((V & kAblTstore) == 0) {
@@ -1116,9 +1206,8 @@ __device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, cons
         }
         // band accumulator of the block being reduced (read early, written at the end)
         double bold = 0.0;
-        const bool acc_on = !RS && rlane && kprev >= 0 && kprev + ridx < nl;
+        const bool acc_on = !RT && rlane && kprev >= 0 && kprev + ridx < nl;
         if (acc_on) bold = bacc[kprev + ridx];
-        if constexpr (RS) red_accumulate(part, slot);
 
         // ---- stage 1: integrand at the block's loaded interfaces, thickness of its layers ------------
         double In[kU], x[kU];
@@ -1126,15 +1215,15 @@ __device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, cons
         for (int m = 0; m < MM; ++m) {
             double qg[kU];
             if (UP)
-                lds_block_m1(lv.qg + m * lv.stride + k0 + kLevShift, qg);
+                lds_f64x8_m1(s_qg + (unsigned)(m * lv.stride + k0 + kLevShift) * 8u, qg);
             else
-                lds_block(lv.qg + m * lv.stride + k0 + 1 + kLevShift, qg);
+                lds_f64x8(s_qg + (unsigned)(m * lv.stride + k0 + 1 + kLevShift) * 8u, qg);
 #pragma unroll
             for (int u = 0; u < kU; ++u) In[u] = m ? fma(qg[u], raw[u][m], In[u]) : qg[u] * raw[u][0];
         }
         {
             double hd[kU];
-            lds_block(lv.hdp + k0, hd);
+            lds_f64x8(s_hdp + (unsigned)k0 * 8u, hd);
 #pragma unroll
             for (int u = 0; u < kU; ++u) {
                 const double lo = UP ? In[u] : (u ? In[u - 1] : Ic);
@@ -1145,77 +1234,29 @@ __device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, cons
         }
         // ---- the next block's table values (or the next pass's first block) into the same registers ----
         if constexpr ((V & kAblLoads) != 0) {
-        } else if (!last) {
+        } else if (it + 1 < nb) {
 #pragma unroll
             for (int m = 0; m < MM; ++m) {
                 unsigned off[kU];
-                lds_block(offs + m * lv.stride + k0 + kstep + 4, off);
+                lds_u32x8(s_offs + (unsigned)(m * lv.stride + k0 + kstep + 4) * 4u, off);
 #pragma unroll
                 for (int u = 0; u < kU; ++u) raw[u][m] = *(const double *)(src_bytes + (size_t)off[u] * 16u);
             }
         } else if (next_src) {
             prefetch_pass<double, MM>(!UP, Lp, next_src, lv, fd);
         }
+        // ---- kVarRedTmem: the previous block's values, transposed, are on their way behind the exp ------
+        uint32_t q0[8], q1[8];
+        double2 cacc = make_double2(0.0, 0.0);
+        if constexpr (RT) {
+            red_fetch(ra.scratch, q0, q1);
+            cacc = red_slot_load(slot);
+        }
 
-        // ---- exp of the block's eight layers, with the previous block's reduction in between ----------
+        // ---- exp of the block's eight layers, with the previous block's shuffle reduction in between ----
         double t[kU];
-        constexpr bool RED = (V & kAblReduce) == 0 && !RS;
-        if constexpr ((V & kVarSwPoly) != 0) {
-            double tn[kU], r[kU], p[kU];
-            int n[kU];
-#pragma unroll
-            for (int u = 0; u < kU; ++u) {
-                int hi = __double2hiint(x[u]);
-                asm("min.s32 %0, %0, 0x40862000;" : "+r"(hi));
-                x[u] = __hiloint2double(hi, __double2loint(x[u]));
-                tn[u] = fma(-x[u], kExpC[11], kExpC[12]);
-            }
-            if constexpr (RED)
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const double keep = h4 ? v[i + 4] : v[i], send = h4 ? v[i] : v[i + 4];
-                a4[i] = keep + __shfl_xor_sync(full, send, 16);
-            }
-#pragma unroll
-            for (int u = 0; u < kU; ++u) {
-                n[u] = __double2loint(tn[u]);
-                tn[u] -= kExpC[12];
-            }
-#pragma unroll
-            for (int u = 0; u < kU; ++u) r[u] = fma(tn[u], kExpC[13], -x[u]);
-#pragma unroll
-            for (int u = 0; u < kU; ++u) {
-                r[u] = fma(tn[u], kExpC[14], r[u]);
-                p[u] = kExpC[0];
-            }
-#pragma unroll
-            for (int i = 1; i <= 10; ++i) {
-#pragma unroll
-                for (int u = 0; u < kU; ++u) p[u] = fma(p[u], r[u], kExpC[i]);
-                if constexpr (RED) {
-                    if (i == 2) {
-#pragma unroll
-                        for (int q = 0; q < 2; ++q) {
-                            const double keep = h3 ? a4[q + 2] : a4[q], send = h3 ? a4[q] : a4[q + 2];
-                            a2[q] = keep + __shfl_xor_sync(full, send, 8);
-                        }
-                    }
-                    if (i == 4) {
-                        const double keep = h2 ? a2[1] : a2[0], send = h2 ? a2[0] : a2[1];
-                        c1 = keep + __shfl_xor_sync(full, send, 4);
-                    }
-                    if (i == 6) c1 += __shfl_xor_sync(full, c1, 2);
-                    if (i == 8) c1 += __shfl_xor_sync(full, c1, 1);
-                }
-            }
-#pragma unroll
-            for (int u = 0; u < kU; ++u) {
-                p[u] = fma(p[u], r[u], kExpC[10]);
-                int hi;
-                asm("mad.lo.s32 %0, %1, 1048576, %2;" : "=r"(hi) : "r"(n[u]), "r"(__double2hiint(p[u])));
-                t[u] = __hiloint2double(hi, __double2loint(p[u]));
-            }
-        } else {
+        constexpr bool RED = (V & kAblReduce) == 0 && !RT;
+        {
         double tn[kU], r[kU], r2[kU], p[kU], Tj[kU];
         int nn[kU];
 #pragma unroll
@@ -1226,7 +1267,7 @@ __device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, cons
             tn[u] = fma(-x[u], kK, kMagic);
         }
         constexpr bool XP = (V & kAblExp) == 0;
-        if constexpr (!RED && !RS) c1 = ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
+        if constexpr (!RED && !RT) c1 = ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
         if constexpr (RED)
 #pragma unroll
         for (int i = 0; i < 4; ++i) {                                    // reduction step 1 (xor 16)
@@ -1238,7 +1279,7 @@ __device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, cons
         for (int u = 0; u < kU; ++u) {
             nn[u] = __double2loint(tn[u]);
             tn[u] -= kMagic;
-            Tj[u] = xl_lookup(nn[u], xaux.saddr);
+            Tj[u] = xl_scale(xl_lookup(nn[u], xaux.saddr), nn[u]);       // 2^(j/512) 2^n
         }
         if constexpr (XP)
 #pragma unroll
@@ -1264,15 +1305,18 @@ __device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, cons
         for (int u = 0; u < kU; ++u) p[u] = fma(r2[u], p[u], r[u]);
         if constexpr (RED) c1 += __shfl_xor_sync(full, c1, 2);           // step 4
 #pragma unroll
-        for (int u = 0; u < kU; ++u) t[u] = XP ? xl_scale(fma(Tj[u], p[u], Tj[u]), nn[u]) : tn[u];
+        for (int u = 0; u < kU; ++u) t[u] = XP ? fma(Tj[u], p[u], Tj[u]) : tn[u];
         if constexpr (RED) c1 += __shfl_xor_sync(full, c1, 1);           // step 5
-
         }
 
         // ---- both recurrences in sweep order; the block's values for the next iteration's reduction ---
         double tR[kU];
-        if constexpr ((V & kAblTstore) == 0) tmem::wait_ld<NW>(tRw);
+        if constexpr (RT)
+            tmem::wait_ld_three(tRw, q0, q1);
+        else if constexpr ((V & kAblTstore) == 0)
+            tmem::wait_ld<NW>(tRw);
         tmem::unpack<kU>(tRw, tR);
+        if constexpr (RT) red_accumulate(q0, q1, cacc, slot);
 #pragma unroll
         for (int o = 0; o < kU; ++o) {
             const int u = UP ? kU - 1 - o : o;
@@ -1280,26 +1324,27 @@ __device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, cons
             ER *= tR[u];
             v[u] = EF + ER;
         }
-        if constexpr ((V & kAblTstore) == 0) {
-            uint32_t tw[NW];
-            tmem::pack<kU>(t, tw);
-            tmem::st<NW>(tst.taddr + (uint32_t)(k0 * 2), tw);
-        }
+        if constexpr ((V & kAblTstore) == 0) tm_store_block<SMALL>(tst.taddr + (uint32_t)(k0 * 2), t);
         if (acc_on) bacc[kprev + ridx] = bold + c1;
         kprev = k0;
-        if constexpr (RS) {
-            red_exchange(v, ra, part);
-            slot = (UP ? ra.up_lane : ra.dn_lane) + k0;
+        if constexpr (RT) {
+            red_park<SMALL>(v, ra.scratch);
+            slot = cbase + k0 * 64;
         }
     }
-    // ---- reduction of the last block ------------------------------------------------------------------
-    if constexpr (RS) {
-        red_accumulate(part, slot);
+
+    // ---- lane sum of the last block -------------------------------------------------------------------
+    if constexpr (RT) {
+        uint32_t q0[8], q1[8];
+        red_fetch(ra.scratch, q0, q1);              // its wait::st also covers the t-store: the next pass reads it back
+        const double2 cacc = red_slot_load(slot);
+        tmem::wait_ld_pair(q0, q1);
+        red_accumulate(q0, q1, cacc, slot);
     } else {
         const double c = reduce8<double>(v, lane);
         if (rlane && kprev + ridx < nl) bacc[kprev + ridx] += c;
+        tmem::wait_st();
     }
-    tmem::wait_st();
 }
 
 template <typename Real, int MM, bool FRESH, int V>
@@ -1323,12 +1368,12 @@ __device__ __forceinline__ void dispatch_pass(const bool lw, const bool up, cons
                 sw_fresh_pass<MM, true, V>(lane, nl, Lp, wF, wR, bg, src_lane, next_src, fd, lv, tst, bacc_up, tabT, ra);
             else
                 sw_fresh_pass<MM, false, V>(lane, nl, Lp, wF, wR, bs, src_lane, next_src, fd, lv, tst, dn, tabT, ra);
-        } else if constexpr (!FRESH && MM > 0 && sizeof(Real) == 8 && (V & kVarSwDirect) != 0 && (V & kVarRedSmem) != 0) {
+        } else if constexpr (!FRESH && MM > 0 && sizeof(Real) == 8 && (V & kVarSwDirect) != 0 && (V & kVarRedTmem) != 0) {
             if (next_src) prefetch_pass<Real, MM>(!up, Lp, next_src, lv, fd);
             if (up)
-                sw_replay_pass<true>(Lp, (double)wR, (double)bg, *reinterpret_cast<const TStore<double> *>(&tst), ra);
+                sw_replay_pass<true, (V & kVarSmallSt) != 0>(Lp, (double)wR, (double)bg, *reinterpret_cast<const TStore<double> *>(&tst), ra);
             else
-                sw_replay_pass<false>(Lp, (double)wR, (double)bs, *reinterpret_cast<const TStore<double> *>(&tst), ra);
+                sw_replay_pass<false, (V & kVarSmallSt) != 0>(Lp, (double)wR, (double)bs, *reinterpret_cast<const TStore<double> *>(&tst), ra);
         } else if (up)
             sweep_pass<Real, MM, false, true, FRESH, V>(lane, nl, Lp, wF, wR, bg, src_lane, next_src, fd, lv, tst, bacc_up, coef, coef, tabT);
         else
@@ -1341,7 +1386,6 @@ __device__ __forceinline__ void dispatch_pass(const bool lw, const bool up, cons
 // with c < ctas_per_col; warp w of the CTA sweeps part c * W + w of the column.
 template <typename Real, int MM, int V = 0>
 __global__ void __launch_bounds__(variant_threads(V), 1) flux_kernel(const FluxArgs<Real> a) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr bool FUSED = MM > 0;
     constexpr int MR = MM > 0 ? MM : 1;
     constexpr bool TM = (V & kVarTmem) != 0, CS = (V & kVarCoefSmem) != 0, PA = (V & kVarPartial) != 0;
@@ -1350,7 +1394,7 @@ __global__ void __launch_bounds__(variant_threads(V), 1) flux_kernel(const FluxA
     const int L = a.L, nl = a.L - 1, Lp = padded_layers(a.L), LS = Lp + kU, C = a.ctas_per_col;
 
     const int ts_rows = (V & kVarMixed) ? Lp - a.tm_rows : -1;     // t-store layers in shared memory
-    const CtaSmem<Real, MM, V> lay(L, ts_rows);
+    const CtaSmem<Real, MM, V> lay(L, ts_rows, a.B);
     unsigned *lev_offdn = (unsigned *)(smem_raw + lay.off_offdn);
     unsigned *lev_offup = (unsigned *)(smem_raw + lay.off_offup);
     Real *lev_qg = (Real *)(smem_raw + lay.off_qg);
@@ -1360,7 +1404,12 @@ __global__ void __launch_bounds__(variant_threads(V), 1) flux_kernel(const FluxA
     double *bacc_up = (double *)(wbase + lay.warp_bacc);
     double *bacc_dn = bacc_up + (PA ? Lp * kPartialLanes : LS);
     const int n_bacc = PA ? 2 * Lp * kPartialLanes : 2 * LS;      // accumulator doubles per warp
-    Real *cw = (Real *)(wbase + lay.warp_coef);                   // staged coefficient rows (kVarCoefSmem)
+    constexpr bool RT = (V & kVarRedTmem) != 0;
+    constexpr unsigned kXlWindow = xl_window(V);
+    const unsigned smem_window0 = (unsigned)__cvta_generic_to_shared(smem_raw);      // shared-window address of smem_raw
+    // staged coefficient rows (kVarCoefSmem): in the warp's region, or (kVarRedTmem) above the exp table
+    Real *cw = RT ? (Real *)(smem_raw + (kXlWindow + kXlBytes - smem_window0) + (size_t)warp * lay.coef_bytes)
+                  : (Real *)(wbase + lay.warp_coef);
     Real *ts = (Real *)(wbase + lay.warp_ts);
     double *sacc = (double *)(smem_raw + lay.shared_total + lay.warp_bacc);   // warp 0's accumulators, free in the epilogue
     Real *coef_cta = a.coefbuf + (size_t)blockIdx.x * a.B * 4 * Lp;
@@ -1374,31 +1423,30 @@ __global__ void __launch_bounds__(variant_threads(V), 1) flux_kernel(const FluxA
     // exp tables: this lane's entry of the 2^(j/32) table (kVarExpTable); the replicated 2^(j/512) table (kVarExpLds)
     double *xtab = (double *)(smem_raw + lay.off_xtab);
     if constexpr ((V & kVarSwDirect) != 0)      // the table sits at shared-window address kXlWindow (launch_flux sizes the window)
-        xtab = (double *)(smem_raw + (kXlWindow - (unsigned)__cvta_generic_to_shared(smem_raw)));
+        xtab = (double *)(smem_raw + (kXlWindow - smem_window0));
     if constexpr ((V & (kVarExpLds | kVarSwDirect)) != 0)
         for (int i = tid; i < kXlN * kXlCopies; i += nthr) xtab[i] = a.exp_tab[i / kXlCopies];
     const ExpAux tabT{kExpTab[lane], xtab + (lane & (kXlCopies - 1)), kXlWindow | ((unsigned)(lane & (kXlCopies - 1)) << 3)};
-    // kVarRedSmem: this warp's group accumulators and exchange scratch, above the exp table in the shared window
-    constexpr bool RS = (V & kVarRedSmem) != 0;
-    RedAux ra{nullptr, nullptr, nullptr, nullptr};
-    double *b4 = nullptr;
-    const int LS4 = red_ls4(Lp);
-    if constexpr (RS) {
-        b4 = (double *)(smem_raw + (2 * kXlWindow - (unsigned)__cvta_generic_to_shared(smem_raw)) + (size_t)warp * red_warp_bytes(Lp));
-        double *red = b4 + 8 * LS4;
-        const int g = lane >> 3, c = lane & 7;
-        ra.up_lane = b4 + g * LS4 + c;
-        ra.dn_lane = b4 + (4 + g) * LS4 + c;
-        ra.st_row = red + lane * kRedStride;
-        ra.ld_col = red + (16 * (g >> 1) + 4 * (g & 1)) * kRedStride + c;
-        for (int i = lane; i < 8 * LS4 + 32 * kRedStride; i += 32) b4[i] = 0.0;
+    // kVarRedTmem: this warp's class accumulators [2][Lp / kU][4][8] double2 and its 16 exchange columns in tensor memory
+    RedAux ra{0u, 0u, 0u};
+    double2 *pacc = nullptr;
+    const int n_pacc = 2 * Lp * 4;                  // double2 per warp, both directions
+    if constexpr (RT) {
+        pacc = (double2 *)(wbase + lay.warp_pacc);
+        ra.up = (unsigned)__cvta_generic_to_shared(pacc + lane);
+        ra.dn = ra.up + (unsigned)Lp * 64u;
+        for (int i = lane; i < n_pacc; i += 32) pacc[i] = make_double2(0.0, 0.0);
     }
     if constexpr (TM) {
         if (warp == 0) tmem::acquire(&s_tmem_base, (uint32_t)a.tmem_cols);
         tmem::fence_before_sync();
         __syncthreads();
         tmem::fence_after_sync();
-        tst.taddr = tmem::address(s_tmem_base, warp, (warp >> 2) * a.tmem_cpw);
+        // (shuffled from lane 0 so that ptxas knows the addresses are warp-uniform: every LDTM / STTM then takes its
+        // address from one uniform register + immediate instead of a fresh R2UR each)
+        tst.taddr = __shfl_sync(0xffffffffu, tmem::address(s_tmem_base, warp, (warp >> 2) * a.tmem_cpw), 0);
+        if constexpr (RT)
+            ra.scratch = __shfl_sync(0xffffffffu, tmem::address(s_tmem_base, warp, (W >> 2) * a.tmem_cpw + (warp >> 2) * 2 * kU), 0);
         uint32_t zero[NW];
 #pragma unroll
         for (int i = 0; i < NW; ++i) zero[i] = 0u;
@@ -1443,6 +1491,15 @@ __global__ void __launch_bounds__(variant_threads(V), 1) flux_kernel(const FluxA
         // ---- emission coefficients of the long-wave bands this CTA touches (real_gas.py:634-638) -----
         const int sA = a.part_seg0[cpart * W], sB = a.part_seg0[(cpart + 1) * W];
         const double Tg = a.T_g[col];
+        const double albedo = a.albedo ? a.albedo[col] : a.albedo_scalar;
+        const double solar = a.star_geom * (1.0 - albedo) / 4.0;  // (R*/d)^2 (1-albedo)/4, :640-642
+        double *bsrc = (double *)(smem_raw + lay.off_bsrc);       // kVarRedTmem: boundary sources of every band, once per column
+        if constexpr (RT)
+            for (int j = tid; j < a.B; j += nthr) {
+                const double c = __ldg(a.band_centre + j);
+                bsrc[j] = M_PI * planck_wavenumber(a.pc, c, Tg);                          // :638
+                bsrc[a.B + j] = M_PI * planck_wavenumber(a.pc, c, a.T_star) * solar;      // :640-642
+            }
         if (sA < sB) {
             // Lane = one layer of a 31-layer chunk (lane 31 only supplies B at the next interface); the
             // warps that share a chunk take every other long-wave band.  Temperatures and the pressure
@@ -1491,8 +1548,6 @@ __global__ void __launch_bounds__(variant_threads(V), 1) flux_kernel(const FluxA
         __syncthreads();
 
         // ---- this warp's run of segments -------------------------------------------------------------
-        const double albedo = a.albedo ? a.albedo[col] : a.albedo_scalar;
-        const double solar = a.star_geom * (1.0 - albedo) / 4.0;  // (R*/d)^2 (1-albedo)/4, :640-642
         const double *tau_col = FUSED ? nullptr : a.tau + (int64_t)(a.tau_id ? a.tau_id[col] : 0) * L * a.N;
         const int part = cpart * W + warp;
         int s = a.part_seg0[part];
@@ -1520,12 +1575,18 @@ __global__ void __launch_bounds__(variant_threads(V), 1) flux_kernel(const FluxA
         }
         while (s < s1) {
             const int j = a.seg_band[s];
-            int e = s + 1;
-            while (e < s1 && a.seg_band[e] == j) ++e;
-            const double c = a.band_centre[j];
-            const bool lw = !a.band_sw[j];
-            const Real bg = (Real)(M_PI * planck_wavenumber(a.pc, c, Tg));                   // :638
-            const Real bs = (Real)(M_PI * planck_wavenumber(a.pc, c, a.T_star) * solar);     // :640-642
+            // the run ends with the band (its remaining chains, 32 per segment) or with this warp's share
+            const int e = min(s1, s + ((__ldg(a.band_len + j) - __ldg(a.seg_c0 + s) + 31) >> 5));
+            const bool lw = !__ldg(a.band_sw + j);
+            Real bg, bs;
+            if constexpr (RT) {
+                bg = (Real)bsrc[j];
+                bs = (Real)bsrc[a.B + j];
+            } else {
+                const double c = a.band_centre[j];
+                bg = (Real)(M_PI * planck_wavenumber(a.pc, c, Tg));                   // :638
+                bs = (Real)(M_PI * planck_wavenumber(a.pc, c, a.T_star) * solar);     // :640-642
+            }
             const Real *coef = coef_cta + (size_t)j * 4 * Lp;
             if constexpr (CS) {          // stage the band's four coefficient rows in this warp's shared memory
                 if (lw) {
@@ -1535,7 +1596,7 @@ __global__ void __launch_bounds__(variant_threads(V), 1) flux_kernel(const FluxA
                 coef = cw;
             }
             // boundary terms: Trans(i,i) = sum of the nu-weights
-            const bool first_chain = a.seg_c0[s] == 0;
+            const bool first_chain = __ldg(a.seg_c0 + s) == 0;
             const double bnd_up = first_chain ? (double)bg * a.band_sumw[j] : 0.0;
             const double bnd_dn = first_chain ? (double)bs * a.band_sumw[j] : 0.0;
             if (!PA && first_chain && lane == 0) {
@@ -1576,21 +1637,31 @@ __global__ void __launch_bounds__(variant_threads(V), 1) flux_kernel(const FluxA
                     o[i] = su;
                     o[L + i] = sd;
                 }
-            } else if constexpr (RS) {
-                // group accumulators: indexed by layer; an upward layer k is interface k (padding layers >= nl
-                // hold junk), a downward layer k interface k + 1
+            } else if constexpr (RT) {
+                // class accumulators of the short-wave passes: indexed by layer; an upward layer k is interface k
+                // (padding layers >= nl hold junk), a downward layer k interface k + 1.  Slot of layer k, class c:
+                // (k / 8) * 32 + (k & 3) + 4 c, .x for k % 8 < 4, .y otherwise; classes added in order.
                 for (int i = lane; i < L; i += 32) {
                     double su = bacc_up[i], sd = bacc_dn[i];
+                    if (!lw) {
+                        if (i < nl) {
+                            const double2 *pu = pacc + (i >> 3) * 32 + (i & 3);
 #pragma unroll
-                    for (int g = 0; g < 4; ++g) {
-                        if (i < nl) su += b4[g * LS4 + i];
-                        if (i >= 1) sd += b4[(4 + g) * LS4 + i - 1];
+                            for (int c = 0; c < 8; ++c) su += (i & 4) ? pu[4 * c].y : pu[4 * c].x;
+                        }
+                        if (i >= 1) {
+                            const int k = i - 1;
+                            const double2 *pd = pacc + Lp * 4 + (k >> 3) * 32 + (k & 3);
+#pragma unroll
+                            for (int c = 0; c < 8; ++c) sd += (k & 4) ? pd[4 * c].y : pd[4 * c].x;
+                        }
                     }
                     o[i] = su;
                     o[L + i] = sd;
                 }
                 __syncwarp();
-                for (int i = lane; i < 8 * LS4; i += 32) b4[i] = 0.0;
+                if (!lw)
+                    for (int i = lane; i < n_pacc; i += 32) pacc[i] = make_double2(0.0, 0.0);
             } else {
                 for (int i = lane; i < L; i += 32) {
                     o[i] = bacc_up[i];

@@ -21,6 +21,7 @@ struct Partition {
     int ctas_per_col = 1;   // C: CTAs sharing a column
     int parts = 0;          // C * W contiguous, cost-balanced runs of segments per column
     int n_slots = 0;        // partial-sum slots per column: one per (part, band) run
+    int cost_model = -1;    // which kernel family the segment costs were fitted to (flux.cu:pass_costs)
     DevBuf<int32_t> part_seg0, part_slot0, band_slot0;
     DevBuf<double> slot_delta;
 };

@@ -119,6 +119,34 @@ __device__ __forceinline__ void wait_ld_all(uint32_t (&r)[NW]) {
     }
 }
 
+// Transposing load, shape 16x256b.x2: the warp reads 16 columns of 16 consecutive TMEM lanes starting at the lane
+// in addr (its quarter's first lane, or that + 16); thread t receives columns 2 (t % 4), 2 (t % 4) + 1 of lane
+// t / 4 (r[0], r[1]) and of lane t / 4 + 8 (r[2], r[3]), and columns 8 + 2 (t % 4), 9 + 2 (t % 4) of the same two
+// lanes (r[4..7]).  With FP64 values parked by st<16> (value u = columns 2 u, 2 u + 1 of the owner's lane) that is
+// value t % 4 (r[0..3]) and value t % 4 + 4 (r[4..7]) of lanes t / 4 and t / 4 + 8.
+__device__ __forceinline__ void ld_16x256b_x2(uint32_t addr, uint32_t (&r)[8]) {
+    asm volatile("tcgen05.ld.sync.aligned.16x256b.x2.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                 : "r"(addr));
+}
+// Wait for every outstanding tcgen05.ld of the thread: two transposed blocks, or those and a block of 16 words.
+__device__ __forceinline__ void wait_ld_pair(uint32_t (&a)[8], uint32_t (&b)[8]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(a[0]), "+r"(a[1]), "+r"(a[2]), "+r"(a[3]), "+r"(a[4]), "+r"(a[5]), "+r"(a[6]), "+r"(a[7]),
+                   "+r"(b[0]), "+r"(b[1]), "+r"(b[2]), "+r"(b[3]), "+r"(b[4]), "+r"(b[5]), "+r"(b[6]), "+r"(b[7])
+                 :
+                 : "memory");
+}
+__device__ __forceinline__ void wait_ld_three(uint32_t (&r)[16], uint32_t (&a)[8], uint32_t (&b)[8]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                   "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]),
+                   "+r"(a[0]), "+r"(a[1]), "+r"(a[2]), "+r"(a[3]), "+r"(a[4]), "+r"(a[5]), "+r"(a[6]), "+r"(a[7]),
+                   "+r"(b[0]), "+r"(b[1]), "+r"(b[2]), "+r"(b[3]), "+r"(b[4]), "+r"(b[5]), "+r"(b[6]), "+r"(b[7])
+                 :
+                 : "memory");
+}
+
 // kU reals <-> 32-bit words (register renames, no instructions).
 template <int N>
 __device__ __forceinline__ void pack(const double (&v)[N], uint32_t (&w)[2 * N]) {
