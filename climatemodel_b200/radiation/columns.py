@@ -79,13 +79,20 @@ class ColumnStepper:
         return self.delta_net_flux
 
     def evolve_to_equilibrium(self, flux_thresh=1e-3, convective_adjust=False, t_end=4.0, conv_thresh=1e-5,
-                              conv_t_multiplier=5, max_steps=1000000, check_every=16):
+                              conv_t_multiplier=5, max_steps=1000000, check_every=16, use_graph=True):
         """``Atmosphere.evolve_to_equilibrium`` (base.py:266-335) for every column at once: all columns
         step together, and a column stops -- is frozen on the device, its T, t and step state left as
         they are -- as soon as ITS equilibrium test holds: max|net flux| or delta_net_flux below its
         threshold (base.py:248-264; the threshold drops to 0.99 delta_net_flux of the column's second
         step, base.py:315-316) or more than t_end years of model time.  The tests run on the device
         with no host round trip; the host looks at the "all done" flag every check_every steps.
+
+        use_graph: after the first two steps (which differ: the threshold update) one whole step --
+        flux kernels, adaptive step, convective adjustment, equilibrium test, freeze mask -- is captured
+        into a CUDA graph and replayed, so a step costs one launch instead of ~20 (a small ensemble is
+        launch-latency bound).  Same kernels on the same data in the same order: results are identical
+        to the eager loop.
+
         Returns the number of steps each column took (int64 tensor).  Raises ValueError when a
         temperature goes negative (base.py:319-320) or max_steps is hit."""
         import torch
@@ -100,29 +107,63 @@ class ColumnStepper:
             whole = torch.floor(full_days / 365)
             return whole + (full_days - 365 * whole) / 365
         years0 = years(self.t)
+
+        def one_step(update_threshold=False):           # every tensor it touches lives outside: replayable
+            running = done == 0
+            dnf = self.step(convective_adjust=convective_adjust, conv_thresh=conv_thresh,
+                            conv_t_multiplier=conv_t_multiplier)
+            n_steps.add_(running)
+            if update_threshold:
+                thr.copy_(torch.minimum(thr, 0.99 * dnf))
+            eq = (self.out['net'].abs().amax(dim=1) < thr) | (dnf < thr) | (years(self.t) - years0 > t_end)
+            done.bitwise_or_((eq & running).to(torch.uint8))
+
+        def host_check(i):
+            if float(self.T.min()) < 0:
+                raise ValueError('Temperature is below zero')
+            if bool(done.all()):
+                return True
+            if i >= max_steps:
+                raise ValueError('no equilibrium after %d steps' % max_steps)
+            return False
+
         check(self._lib.cmb200_stepper_set_frozen(self._h, C.c_void_p(done.data_ptr())))
+        graph = None
         try:
             i = 0
-            while True:
-                running = done == 0
-                dnf = self.step(convective_adjust=convective_adjust, conv_thresh=conv_thresh,
-                                conv_t_multiplier=conv_t_multiplier)
-                n_steps += running
-                if i == 1:
-                    thr = torch.minimum(thr, 0.99 * dnf)
-                eq = (self.out['net'].abs().amax(dim=1) < thr) | (dnf < thr) | (years(self.t) - years0 > t_end)
-                done |= (eq & running).to(torch.uint8)
+            while i < 2 and i < max_steps:              # eager: warm-up of every buffer, and the step that sets thr
+                one_step(update_threshold=(i == 1))
                 i += 1
-                if i % check_every == 0 or i >= max_steps:
-                    if float(self.T.min()) < 0:
-                        raise ValueError('Temperature is below zero')
-                    if bool(done.all()):
-                        break
+            finished = host_check(i)
+            if not finished and use_graph:
+                try:
+                    side = torch.cuda.Stream(device=dev)
+                    side.wait_stream(torch.cuda.current_stream(dev))
+                    with torch.cuda.stream(side):
+                        one_step()                      # on the capture stream once, outside the capture
+                        i += 1
+                    torch.cuda.current_stream(dev).wait_stream(side)
+                    graph = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(graph, stream=side):
+                        one_step()
+                except Exception:                       # capture refused (e.g. an allocation inside): eager loop
+                    graph = None
+                    torch.cuda.synchronize(dev)
+            while not finished:
+                for _ in range(check_every):
+                    if graph is not None:
+                        graph.replay()
+                    else:
+                        one_step()
+                    i += 1
                     if i >= max_steps:
-                        raise ValueError('no equilibrium after %d steps' % max_steps)
+                        break
+                finished = host_check(i)
         finally:
             torch.cuda.current_stream(dev).synchronize()
             check(self._lib.cmb200_stepper_set_frozen(self._h, None))
+            del graph
+        self.graph_replayed = use_graph
         return n_steps
 
     @property
