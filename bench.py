@@ -308,17 +308,23 @@ def rce_record(torch, plan, w, dev, n_col, n_steps=24):
     qe = np.empty((2, n, L))
     qe[0] = synthetic.co2_mass_ratio(ppmv)[:, None]
     qe[1] = 0.005 * (P[None, :] / P[-1]) ** 3
-    ens = ColumnStepper(plan, t(np.repeat(Tg[:, None], L - 1, axis=1)), t(Tg), q=t(qe),
-                        T_tau=t(np.repeat(Tg[:, None], L, axis=1)), albedo=0.3)
-    torch.cuda.synchronize()
-    l0, t0 = _lib.launch_count(), time.perf_counter()
-    steps = ens.evolve_to_equilibrium(flux_thresh=1e-3, convective_adjust=True, t_end=4.0, max_steps=200000)
-    torch.cuda.synchronize()
-    wall = time.perf_counter() - t0
+    for trial in range(2):                              # the first run pays the one-time set-up of this column count
+        ens = ColumnStepper(plan, t(np.repeat(Tg[:, None], L - 1, axis=1)), t(Tg), q=t(qe),
+                            T_tau=t(np.repeat(Tg[:, None], L, axis=1)), albedo=0.3)
+        torch.cuda.synchronize()
+        l0, t0 = _lib.launch_count(), time.perf_counter()
+        steps = ens.evolve_to_equilibrium(flux_thresh=1e-3, convective_adjust=True, t_end=4.0, max_steps=200000)
+        torch.cuda.synchronize()
+        wall = time.perf_counter() - t0
     surf = ens.T[:, -1].cpu().numpy()
+    flux128, _ = time_flux(torch, plan, [t(x) for x in (np.repeat(Tg[:, None], L - 1, axis=1), Tg, np.repeat(Tg[:, None], L, axis=1),
+                                                       qe, np.full(n, 0.3))], n, 5)
     rec['ensemble'] = {'workload': 'RCE CO2-doubling ensemble over latitude (BASELINE configs[4])', 'columns': int(n),
                        'wall_s': wall, 'column_steps': int(steps.sum()), 'max_steps_of_a_column': int(steps.max()),
                        'column_steps_per_s': float(steps.sum()) / wall, 'ms_per_ensemble_step': 1e3 * wall / int(steps.max()),
+                       'bare_flux_ms_128_columns': flux128,
+                       'bound': 'the flux evaluation of one column per SM (128 columns on 148 SMs): a step cannot be shorter than '
+                                'one column on one SM; launches are not the limit (a CUDA-graph replay of the whole step measures the same)',
                        'gpu_launches': int(_lib.launch_count() - l0),
                        'dT_lowest_layer_2xCO2_K_mean': float((surf[1::2] - surf[0::2]).mean())}
     return rec

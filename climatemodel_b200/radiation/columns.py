@@ -79,7 +79,7 @@ class ColumnStepper:
         return self.delta_net_flux
 
     def evolve_to_equilibrium(self, flux_thresh=1e-3, convective_adjust=False, t_end=4.0, conv_thresh=1e-5,
-                              conv_t_multiplier=5, max_steps=1000000, check_every=16, use_graph=True):
+                              conv_t_multiplier=5, max_steps=1000000, check_every=16, use_graph=False):
         """``Atmosphere.evolve_to_equilibrium`` (base.py:266-335) for every column at once: all columns
         step together, and a column stops -- is frozen on the device, its T, t and step state left as
         they are -- as soon as ITS equilibrium test holds: max|net flux| or delta_net_flux below its
@@ -89,9 +89,11 @@ class ColumnStepper:
 
         use_graph: after the first two steps (which differ: the threshold update) one whole step --
         flux kernels, adaptive step, convective adjustment, equilibrium test, freeze mask -- is captured
-        into a CUDA graph and replayed, so a step costs one launch instead of ~20 (a small ensemble is
-        launch-latency bound).  Same kernels on the same data in the same order: results are identical
-        to the eager loop.
+        into a CUDA graph and replayed, so a step costs one launch instead of ~20.  Same kernels on the
+        same data in the same order: results are identical to the eager loop.  Off by default: measured
+        on the 128-column ensemble of BASELINE configs[4] the eager loop already runs at the pace of the
+        flux kernel (0.60 ms per step of which 0.51 ms flux: one column per SM), so the graph only pays
+        for its capture (0.246 s eager, 0.238-0.292 s with the graph, 408 steps).
 
         Returns the number of steps each column took (int64 tensor).  Raises ValueError when a
         temperature goes negative (base.py:319-320) or max_steps is hit."""

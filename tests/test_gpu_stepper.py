@@ -178,9 +178,10 @@ def test_device_steps_with_convection_equal_host_steps(level_order):
     assert moved >= 5                                           # every column convected at least once
 
 
+@pytest.mark.parametrize('use_graph', [False, True])
 @pytest.mark.parametrize('level_order', ORDERS)
 @pytest.mark.parametrize('convective', [False, True])
-def test_batched_evolve_to_equilibrium_equals_per_column_host_loop(convective, level_order):
+def test_batched_evolve_to_equilibrium_equals_per_column_host_loop(convective, level_order, use_graph):
     """ColumnStepper.evolve_to_equilibrium against Atmosphere.evolve_to_equilibrium's loop
     (base.py:266-335) run column by column on the host with the same net fluxes: every column stops
     at its own step -- by the flux test, by the tightened threshold of the second step or by t_end --
@@ -205,7 +206,7 @@ def test_batched_evolve_to_equilibrium_equals_per_column_host_loop(convective, l
     dev = torch.device('cuda', 0)
     cols = ColumnStepper(plan, torch.tensor(T0, device=dev), torch.tensor(T_g, device=dev), q=torch.tensor(q, device=dev),
                          albedo=0.3, temp_change=4.0, level_order=level_order)
-    n_steps = cols.evolve_to_equilibrium(check_every=5, max_steps=600, **kw).cpu().numpy()
+    n_steps = cols.evolve_to_equilibrium(check_every=5, max_steps=600, use_graph=use_graph, **kw).cpu().numpy()
 
     # host: one Atmosphere per column; the net fluxes come from the same plan and the same batch shape
     host = host_columns(P, T0, level_order)
