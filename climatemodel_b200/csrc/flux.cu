@@ -137,7 +137,7 @@ static int variant_warps(int L, int max_smem, int *tmem_cpw, int *tmem_cols, int
             *tm_rows = std::min(Lp, (512 / per_quarter / wpr) / kU * kU);
             ts_rows = Lp - *tm_rows;
         } else {
-            per_quarter = std::min(2, 512 / (Lp * wpr));
+            per_quarter = std::min(variant_threads<Real>(V) / 128, 512 / (Lp * wpr + ((V & kVarRedTmem) ? 2 * kU : 0)));
             *tm_rows = Lp;
         }
         most = 4 * per_quarter;
@@ -167,8 +167,9 @@ static int variant_warps(int L, int max_smem, int *tmem_cpw, int *tmem_cols, int
 constexpr int kReferenceVariant = kVarTmem | kVarCoefSmem;
 template <typename Real, int MM>
 constexpr int default_variant() {
-    if (!std::is_same<Real, double>::value) return kReferenceVariant;
-    return MM > 0 ? (kReferenceVariant | kVarExpLds | kVarSwDirect | kVarRedTmem | kVarSmallSt) : (kReferenceVariant | kVarExpLds);
+    constexpr int direct = kVarSwDirect | kVarRedTmem | kVarSmallSt;      // table-fused path: direct short-wave passes
+    if (!std::is_same<Real, double>::value) return MM > 0 ? (kReferenceVariant | direct) : kReferenceVariant;
+    return MM > 0 ? (kReferenceVariant | kVarExpLds | direct) : (kReferenceVariant | kVarExpLds);
 }
 #ifndef CMB_FLUX_EXPERIMENTS
 #ifdef CMB_DEV_BUILD
@@ -234,7 +235,11 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     // A CTA that allocates tensor memory must be alone on its SM (a second one would wait for the
     // columns): ask for more than half of the shared memory.
     size_t smem = (V & kVarTmem) ? std::max(lay.total(W), (size_t)max_smem / 2 + 1024) : lay.total(W);
-    if constexpr ((V & kVarSwDirect) != 0) {
+    if constexpr ((V & kVarRedTmem) != 0 && !std::is_same<Real, double>::value) {
+        // FP32: no exp table, everything contiguous; the exchange columns follow the t-stores in tensor memory
+        if (lay.total(W) + 1024 > (size_t)max_smem || (W / 4) * (tmem_cpw + 2 * kU) > tmem_cols)
+            return launch_flux<Real, MM, V & ~(kVarSwDirect | kVarRedTmem | kVarSmallSt)>(p, io, Tint, s);
+    } else if constexpr ((V & kVarSwDirect) != 0 && std::is_same<Real, double>::value) {
         // the exp table occupies shared-window addresses [xl_window, xl_window + 64 kB): the level tables and the
         // warps' regions have to end below it (the window starts at a small driver-reserved offset)
         constexpr unsigned win = xl_window(V);
@@ -411,7 +416,7 @@ static int launch_flux_variant(int variant, cmb200_plan *plan, const cmb200_flux
     if (variant == 0) return launch_flux<Real, MM, 0>(plan, io, Tint, s);
     if (variant == kReferenceVariant) return launch_flux<Real, MM, kReferenceVariant>(plan, io, Tint, s);
     // the default's own fall-back (shuffle reduction instead of the tensor-memory transpose) is compiled anyway: A/B
-    if constexpr ((default_variant<Real, MM>() & kVarRedTmem) != 0)
+    if constexpr ((default_variant<Real, MM>() & kVarRedTmem) != 0 && std::is_same<Real, double>::value)
         if (variant == (default_variant<Real, MM>() & ~(kVarRedTmem | kVarSmallSt)))
             return launch_flux<Real, MM, default_variant<Real, MM>() & ~(kVarRedTmem | kVarSmallSt)>(plan, io, Tint, s);
     return launch_flux<Real, MM, default_variant<Real, MM>()>(plan, io, Tint, s);

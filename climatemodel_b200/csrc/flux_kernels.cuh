@@ -131,7 +131,12 @@ struct ExpAux {
 // first block, the exp polynomial, the warp reduction, the t-store traffic.
 constexpr int kAblLoads = 64, kAblExp = 128, kAblReduce = 256, kAblTstore = 512;
 constexpr int kPartialLanes = 8;
-constexpr int variant_threads(int V) { return (V & kVarMixed) ? 384 : 256; }
+// Threads per CTA the kernel is compiled for: 8 warps, or 12 (168 registers) for kVarMixed and for the FP32 direct
+// passes, whose t-stores are half as wide (three warps per lane quarter of tensor memory instead of two).
+template <typename Real>
+constexpr int variant_threads(int V) {
+    return ((V & kVarMixed) || (sizeof(Real) == 4 && (V & 8192))) ? 384 : 256;
+}
 
 constexpr int kU = 8;          // layers per block of a pass (instruction-level parallelism)
 
@@ -219,8 +224,8 @@ struct CtaSmem {
         warp_coef = up16((V & kVarPartial) ? (size_t)2 * Lp * kPartialLanes * sizeof(double)
                                            : (size_t)2 * (Lp + kU) * sizeof(double));
         coef_bytes = (V & kVarCoefSmem) ? (size_t)4 * Lp * sizeof(Real) : 0;
-        if (V & kVarRedTmem) {      // class accumulators here, coefficient rows above the exp table
-            warp_pacc = warp_coef;
+        if (V & kVarRedTmem) {      // class accumulators here; FP64: the coefficient rows go above the exp table
+            warp_pacc = sizeof(Real) == 8 ? warp_coef : up16(warp_coef + coef_bytes);
             warp_ts = up16(warp_pacc + red_warp_bytes(Lp));
         } else {
             warp_pacc = 0;
@@ -1014,9 +1019,9 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
 //   red_fetch  (after the stores have landed) thread (u, c) = (lane & 3, lane >> 2) reads values u and u + 4 of
 //              lanes c, c + 8 (q0) and c + 16, c + 24 (q1); valid after the next tcgen05.wait::ld;
 //   red_accumulate  adds them, lanes in ascending order pairwise, to the thread's class accumulator.
-// A block of kU FP64 values -> 2 kU consecutive columns of the lane: one STTM.x16, or (SMALL) eight STTM.x2 whose
-// operand is the register pair the value was produced in -- ptxas assembles wider operand groups with moves
-// (two per value), a pair never needs one.
+// A block of kU values -> consecutive columns of the lane (two per FP64 value, one per FP32 value): one STTM.x16 /
+// .x8, or (SMALL) one STTM per value whose operand is the register (pair) the value was produced in -- ptxas
+// assembles wider operand groups with moves (two per FP64 value), a single value never needs one.
 template <bool SMALL>
 __device__ __forceinline__ void tm_store_block(uint32_t addr, const double (&v)[kU]) {
     if constexpr (SMALL) {
@@ -1032,13 +1037,39 @@ __device__ __forceinline__ void tm_store_block(uint32_t addr, const double (&v)[
     }
 }
 template <bool SMALL>
-__device__ __forceinline__ void red_park(const double (&v)[kU], uint32_t scratch) {
+__device__ __forceinline__ void tm_store_block(uint32_t addr, const float (&v)[kU]) {
+    if constexpr (SMALL) {
+#pragma unroll
+        for (int u = 0; u < kU; ++u) tmem::st_one(addr + (uint32_t)u, __float_as_uint(v[u]));
+    } else {
+        uint32_t w[kU];
+        tmem::pack<kU>(v, w);
+        tmem::st<kU>(addr, w);
+    }
+}
+template <bool SMALL, typename Real>
+__device__ __forceinline__ void red_park(const Real (&v)[kU], uint32_t scratch) {
     tm_store_block<SMALL>(scratch, v);
 }
-__device__ __forceinline__ void red_fetch(uint32_t scratch, uint32_t (&q0)[8], uint32_t (&q1)[8]) {
+// The transposed values of a parked block: FP64 8 words from lanes c, c + 8 and 8 from c + 16, c + 24 (values u, u + 4,
+// u = lane & 3); FP32 4 + 4 words (values 2 u, 2 u + 1).
+template <typename Real>
+struct RedQ {
+    static constexpr int N = sizeof(Real) == 8 ? 8 : 4;
+    uint32_t q0[N], q1[N];
+};
+__device__ __forceinline__ void red_fetch_issued(uint32_t addr, RedQ<double> &r) {     // the stores have landed already
+    tmem::ld_16x256b_x2(addr, r.q0);
+    tmem::ld_16x256b_x2(addr + (16u << 16), r.q1);
+}
+__device__ __forceinline__ void red_fetch_issued(uint32_t addr, RedQ<float> &r) {
+    tmem::ld_16x256b_x1(addr, r.q0);
+    tmem::ld_16x256b_x1(addr + (16u << 16), r.q1);
+}
+template <typename Real>
+__device__ __forceinline__ void red_fetch(uint32_t scratch, RedQ<Real> &r) {
     tmem::wait_st();
-    tmem::ld_16x256b_x2(scratch, q0);
-    tmem::ld_16x256b_x2(scratch + (16u << 16), q1);
+    red_fetch_issued(scratch, r);
 }
 // (one 128-bit access each way, written as PTX: left to itself nvcc splits the pair into two 64-bit accesses
 // whose 16-byte lane stride costs two extra wavefronts)
@@ -1047,11 +1078,30 @@ __device__ __forceinline__ double2 red_slot_load(unsigned slot) {
     asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(a.x), "=d"(a.y) : "r"(slot));
     return a;
 }
-__device__ __forceinline__ void red_accumulate(const uint32_t (&q0)[8], const uint32_t (&q1)[8], double2 acc, unsigned slot) {
+__device__ __forceinline__ void red_slot_store(unsigned slot, double2 a) {
+    asm volatile("st.shared.v2.f64 [%0], {%1, %2};" ::"r"(slot), "d"(a.x), "d"(a.y) : "memory");
+}
+// Four lanes added pairwise in ascending order, into the class accumulator: .x = value u (FP64) / 2 u (FP32) of the
+// block, .y = value u + 4 / 2 u + 1.  FP32 chains are added in FP32 over the four lanes, in FP64 from there on.
+__device__ __forceinline__ void red_accumulate(const RedQ<double> &r, double2 acc, unsigned slot) {
     auto d = [](const uint32_t(&q)[8], int i) { return __hiloint2double((int)q[2 * i + 1], (int)q[2 * i]); };
-    acc.x += (d(q0, 0) + d(q0, 1)) + (d(q1, 0) + d(q1, 1));
-    acc.y += (d(q0, 2) + d(q0, 3)) + (d(q1, 2) + d(q1, 3));
-    asm volatile("st.shared.v2.f64 [%0], {%1, %2};" ::"r"(slot), "d"(acc.x), "d"(acc.y) : "memory");
+    acc.x += (d(r.q0, 0) + d(r.q0, 1)) + (d(r.q1, 0) + d(r.q1, 1));
+    acc.y += (d(r.q0, 2) + d(r.q0, 3)) + (d(r.q1, 2) + d(r.q1, 3));
+    red_slot_store(slot, acc);
+}
+__device__ __forceinline__ void red_accumulate(const RedQ<float> &r, double2 acc, unsigned slot) {
+    auto f = [](uint32_t w) { return __uint_as_float(w); };
+    acc.x += (double)((f(r.q0[0]) + f(r.q0[2])) + (f(r.q1[0]) + f(r.q1[2])));
+    acc.y += (double)((f(r.q0[1]) + f(r.q0[3])) + (f(r.q1[1]) + f(r.q1[3])));
+    red_slot_store(slot, acc);
+}
+template <typename Real>
+__device__ __forceinline__ void red_wait(RedQ<Real> &r) {
+    tmem::wait_ld_pair(r.q0, r.q1);
+}
+template <typename Real, int NW>
+__device__ __forceinline__ void red_wait(uint32_t (&tw)[NW], RedQ<Real> &r) {
+    tmem::wait_ld_three(tw, r.q0, r.q1);
 }
 
 // Replay-only pass of a short-wave band run (the last segment's chain in the direction it has not been swept
@@ -1059,43 +1109,37 @@ __device__ __forceinline__ void red_accumulate(const uint32_t (&q0)[8], const ui
 // back into the t-store columns its t came from (nobody needs that t again; the next run's first pass replays
 // with weight 0 and only wants finite numbers there).  Lane sums: the whole t-store is then read back with the
 // transposing loads, block after block with nothing serial between them, into the class accumulators.
-template <bool UP, bool SMALL>
-__device__ __forceinline__ void sw_replay_pass(const int Lp, const double wR, const double b0, const TStore<double> tst,
+template <typename Real, bool UP, bool SMALL>
+__device__ __forceinline__ void sw_replay_pass(const int Lp, const Real wR, const Real b0, const TStore<Real> tst,
                                                const RedAux ra) {
-    constexpr int NW = 2 * kU;
+    constexpr int WPR = sizeof(Real) / 4, NW = kU * WPR;
     const int kfirst = UP ? Lp - kU : 0, kstep = UP ? -kU : kU, nb = Lp / kU;
-    double ER = wR * b0;
+    Real ER = wR * b0;
     uint32_t tw[NW];
-    tmem::ld<NW>(tst.taddr + (uint32_t)(kfirst * 2), tw);
+    tmem::ld<NW>(tst.taddr + (uint32_t)(kfirst * WPR), tw);
     for (int it = 0, k0 = kfirst; it < nb; ++it, k0 += kstep) {
-        double tR[kU], v[kU];
+        Real tR[kU], v[kU];
         tmem::wait_ld<NW>(tw);
         tmem::unpack<kU>(tw, tR);
-        if (it + 1 < nb) tmem::ld<NW>(tst.taddr + (uint32_t)((k0 + kstep) * 2), tw);
+        if (it + 1 < nb) tmem::ld<NW>(tst.taddr + (uint32_t)((k0 + kstep) * WPR), tw);
 #pragma unroll
         for (int o = 0; o < kU; ++o) {
             const int u = UP ? kU - 1 - o : o;
             ER *= tR[u];
             v[u] = ER;
         }
-        tm_store_block<SMALL>(tst.taddr + (uint32_t)(k0 * 2), v);
+        tm_store_block<SMALL>(tst.taddr + (uint32_t)(k0 * WPR), v);
     }
     tmem::wait_st();
     const unsigned base = UP ? ra.up : ra.dn;
-    uint32_t q0[8], q1[8];
-    tmem::ld_16x256b_x2(tst.taddr, q0);
-    tmem::ld_16x256b_x2(tst.taddr + (16u << 16), q1);
+    RedQ<Real> q;
+    red_fetch_issued(tst.taddr, q);
     for (int b = 0; b < nb; ++b) {
-        uint32_t p0[8], p1[8];
         const double2 acc = red_slot_load(base + b * 512);
-        tmem::wait_ld_pair(q0, q1);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) p0[i] = q0[i], p1[i] = q1[i];
-        if (b + 1 < nb) {
-            tmem::ld_16x256b_x2(tst.taddr + (uint32_t)((b + 1) * 2 * kU), q0);
-            tmem::ld_16x256b_x2(tst.taddr + (uint32_t)((b + 1) * 2 * kU) + (16u << 16), q1);
-        }
-        red_accumulate(p0, p1, acc, base + b * 512);
+        red_wait(q);
+        const RedQ<Real> p = q;
+        if (b + 1 < nb) red_fetch_issued(tst.taddr + (uint32_t)((b + 1) * NW), q);
+        red_accumulate(p, acc, base + b * 512);
     }
 }
 
@@ -1133,14 +1177,22 @@ __device__ __forceinline__ double xl_scale(double tt, int n) {
 // (LDS with the array's link-time base as immediate); through the generic pointers of LevelView the compiler
 // rebuilds the shared window base (S2UR of the CTA id + shifts) in front of every group of loads.
 extern __shared__ __align__(16) unsigned char smem_raw[];
-__device__ __forceinline__ void lds_f64x8(unsigned off, double (&o)[kU]) {
+__device__ __forceinline__ void lds_real8(unsigned off, double (&o)[kU]) {
 #pragma unroll
     for (int i = 0; i < kU / 2; ++i) {
         const double2 q = *reinterpret_cast<const double2 *>(smem_raw + off + 16u * i);
         o[2 * i] = q.x, o[2 * i + 1] = q.y;
     }
 }
-__device__ __forceinline__ void lds_f64x8_m1(unsigned off, double (&o)[kU]) {      // off + 8 is 16-byte aligned
+__device__ __forceinline__ void lds_real8(unsigned off, float (&o)[kU]) {
+#pragma unroll
+    for (int i = 0; i < kU / 4; ++i) {
+        const float4 q = *reinterpret_cast<const float4 *>(smem_raw + off + 16u * i);
+        o[4 * i] = q.x, o[4 * i + 1] = q.y, o[4 * i + 2] = q.z, o[4 * i + 3] = q.w;
+    }
+}
+// The same for a run that starts one element before a 16-byte boundary.
+__device__ __forceinline__ void lds_real8_m1(unsigned off, double (&o)[kU]) {
     o[0] = *reinterpret_cast<const double *>(smem_raw + off);
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
@@ -1148,6 +1200,14 @@ __device__ __forceinline__ void lds_f64x8_m1(unsigned off, double (&o)[kU]) {   
         o[1 + 2 * i] = q.x, o[2 + 2 * i] = q.y;
     }
     o[7] = *reinterpret_cast<const double *>(smem_raw + off + 56u);
+}
+__device__ __forceinline__ void lds_real8_m1(unsigned off, float (&o)[kU]) {
+    o[0] = *reinterpret_cast<const float *>(smem_raw + off);
+    const float4 q = *reinterpret_cast<const float4 *>(smem_raw + off + 4u);
+    o[1] = q.x, o[2] = q.y, o[3] = q.z, o[4] = q.w;
+    const float2 w = *reinterpret_cast<const float2 *>(smem_raw + off + 20u);
+    o[5] = w.x, o[6] = w.y;
+    o[7] = *reinterpret_cast<const float *>(smem_raw + off + 28u);
 }
 __device__ __forceinline__ void lds_u32x8(unsigned off, unsigned (&o)[kU]) {
 #pragma unroll
@@ -1157,17 +1217,85 @@ __device__ __forceinline__ void lds_u32x8(unsigned off, unsigned (&o)[kU]) {
     }
 }
 
-template <int MM, bool UP, int V>
-__device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, const int Lp, const double wF, const double wR,
-                                              const double b0, const void *src_lane, const void *next_src,
-                                              PassFeed<double, MM> &fd, const LevelView<double> lv,
-                                              const TStore<double> tst, double *bacc, const ExpAux xaux, const RedAux ra) {
-    static_assert(MM > 0, "table-fused path");
-    constexpr bool RT = (V & kVarRedTmem) != 0, SMALL = (V & kVarSmallSt) != 0;
-    constexpr int NW = 2 * kU;
+// exp(-x) of a block for the direct pass.  FP64: the shared-memory table routine (see the variant list), eight
+// evaluations step by step; with RED the five shuffle stages of the previous block's lane sum are issued in between.
+// FP32: ex2.approx, as everywhere in FP32 mode.
+template <int V, bool RED>
+__device__ __forceinline__ void direct_exp(double (&x)[kU], double (&t)[kU], const ExpAux xaux, const int lane,
+                                           const double (&v)[kU], double &c1) {
     constexpr double kK = 0x1.71547652b82fep+9, kMagic = 6755399441055744.0, kC = -0x1.62e42fefa39efp-10;
     const unsigned full = 0xffffffffu;
     const bool h4 = lane & 16, h3 = lane & 8, h2 = lane & 4;
+    double a4[4], a2[2];
+    double tn[kU], r[kU], r2[kU], p[kU], Tj[kU];
+    int nn[kU];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+        int hi = __double2hiint(x[u]);
+        asm("min.s32 %0, %0, 0x40862000;" : "+r"(hi));            // thickness clamp (clamp_thickness), in place
+        x[u] = __hiloint2double(hi, __double2loint(x[u]));
+        tn[u] = fma(-x[u], kK, kMagic);
+    }
+    constexpr bool XP = (V & kAblExp) == 0;
+    if constexpr (RED)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {                                    // reduction step 1 (xor 16)
+        const double keep = h4 ? v[i + 4] : v[i], send = h4 ? v[i] : v[i + 4];
+        a4[i] = keep + __shfl_xor_sync(full, send, 16);
+    }
+    if constexpr (XP)
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+        nn[u] = __double2loint(tn[u]);
+        tn[u] -= kMagic;
+        Tj[u] = xl_scale(xl_lookup(nn[u], xaux.saddr), nn[u]);       // 2^(j/512) 2^n
+    }
+    if constexpr (XP)
+#pragma unroll
+    for (int u = 0; u < kU; ++u) r[u] = fma(tn[u], kC, -x[u]);
+    if constexpr (RED)
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {                                    // step 2 (xor 8)
+        const double keep = h3 ? a4[i + 2] : a4[i], send = h3 ? a4[i] : a4[i + 2];
+        a2[i] = keep + __shfl_xor_sync(full, send, 8);
+    }
+    if constexpr (XP)
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+        r2[u] = r[u] * r[u];
+        p[u] = fma(r[u], 1.0 / 6.0, 0.5);
+    }
+    if constexpr (RED) {                                             // step 3 (xor 4)
+        const double keep = h2 ? a2[1] : a2[0], send = h2 ? a2[0] : a2[1];
+        c1 = keep + __shfl_xor_sync(full, send, 4);
+    }
+    if constexpr (XP)
+#pragma unroll
+    for (int u = 0; u < kU; ++u) p[u] = fma(r2[u], p[u], r[u]);
+    if constexpr (RED) c1 += __shfl_xor_sync(full, c1, 2);           // step 4
+#pragma unroll
+    for (int u = 0; u < kU; ++u) t[u] = XP ? fma(Tj[u], p[u], Tj[u]) : tn[u];
+    if constexpr (RED) c1 += __shfl_xor_sync(full, c1, 1);           // step 5
+}
+template <int V, bool RED>
+__device__ __forceinline__ void direct_exp(float (&x)[kU], float (&t)[kU], const ExpAux, const int lane,
+                                           const float (&v)[kU], float &c1) {
+    // exp(-x) = 2^(-x log2 e): one multiply and one MUFU.EX2.  (__expf wraps ex2.approx in a range test and two more
+    // multiplies so that denormal RESULTS survive; a transmissivity below 1e-38 is zero at any tolerance of this mode.)
+#pragma unroll
+    for (int u = 0; u < kU; ++u) asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(t[u]) : "f"(x[u] * -1.4426950408889634f));
+    if constexpr (RED) c1 = reduce8<float>(v, lane);
+}
+
+template <typename Real, int MM, bool UP, int V>
+__device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, const int Lp, const Real wF, const Real wR,
+                                              const Real b0, const void *src_lane, const void *next_src,
+                                              PassFeed<Real, MM> &fd, const LevelView<Real> lv,
+                                              const TStore<Real> tst, double *bacc, const ExpAux xaux, const RedAux ra) {
+    static_assert(MM > 0, "table-fused path");
+    constexpr bool RT = (V & kVarRedTmem) != 0, SMALL = (V & kVarSmallSt) != 0;
+    constexpr int WPR = sizeof(Real) / 4, NW = kU * WPR;
+    constexpr unsigned kRB = sizeof(Real);
     const int ridx = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
     const bool rlane = (lane & 3) == 0;
     const int kfirst = UP ? Lp - kU : 0, kstep = UP ? -kU : kU, nb = Lp / kU;
@@ -1177,14 +1305,14 @@ __device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, cons
     const unsigned s_offs = (unsigned)__cvta_generic_to_shared(UP ? lv.off_up : lv.off_dn) - s0;
     const unsigned s_qg = (unsigned)__cvta_generic_to_shared(lv.qg) - s0, s_hdp = (unsigned)__cvta_generic_to_shared(lv.hdp) - s0;
 
-    double EF = wF * b0, ER = wR * b0;
-    double Ic = 0.0;
+    Real EF = wF * b0, ER = wR * b0;
+    Real Ic = Real(0);
 #pragma unroll
     for (int m = 0; m < MM; ++m) Ic = fma(lv.qg[m * lv.stride + (UP ? Lp : 0) + kLevShift], fd.icraw[m], Ic);
 
-    double v[kU], a4[4], a2[2], c1 = 0.0;
+    Real v[kU], c1 = Real(0);
 #pragma unroll
-    for (int u = 0; u < kU; ++u) v[u] = 0.0;
+    for (int u = 0; u < kU; ++u) v[u] = Real(0);
     int kprev = -kU * 4;        // block whose values v holds (none yet: its accumulate is predicated off)
     // kVarRedTmem: class accumulator the pending lane sums go to; the first accumulate adds the zeros parked here
     const unsigned cbase = UP ? ra.up : ra.dn;
@@ -1199,10 +1327,10 @@ __device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, cons
         // replay chain's t of this block
         uint32_t tRw[NW];
         if constexpr ((V & kAblTstore) == 0) {
-            tmem::ld<NW>(tst.taddr + (uint32_t)(k0 * 2), tRw);
+            tmem::ld<NW>(tst.taddr + (uint32_t)(k0 * WPR), tRw);
         } else {
 #pragma unroll
-            for (int i = 0; i < NW; ++i) tRw[i] = 0x3ff00000u * (i & 1);
+            for (int i = 0; i < NW; ++i) tRw[i] = WPR == 2 ? 0x3ff00000u * (i & 1) : 0x3f800000u;
         }
         // band accumulator of the block being reduced (read early, written at the end)
         double bold = 0.0;
@@ -1210,24 +1338,24 @@ __device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, cons
         if (acc_on) bold = bacc[kprev + ridx];
 
         // ---- stage 1: integrand at the block's loaded interfaces, thickness of its layers ------------
-        double In[kU], x[kU];
+        Real In[kU], x[kU];
 #pragma unroll
         for (int m = 0; m < MM; ++m) {
-            double qg[kU];
+            Real qg[kU];
             if (UP)
-                lds_f64x8_m1(s_qg + (unsigned)(m * lv.stride + k0 + kLevShift) * 8u, qg);
+                lds_real8_m1(s_qg + (unsigned)(m * lv.stride + k0 + kLevShift) * kRB, qg);
             else
-                lds_f64x8(s_qg + (unsigned)(m * lv.stride + k0 + 1 + kLevShift) * 8u, qg);
+                lds_real8(s_qg + (unsigned)(m * lv.stride + k0 + 1 + kLevShift) * kRB, qg);
 #pragma unroll
             for (int u = 0; u < kU; ++u) In[u] = m ? fma(qg[u], raw[u][m], In[u]) : qg[u] * raw[u][0];
         }
         {
-            double hd[kU];
-            lds_f64x8(s_hdp + (unsigned)k0 * 8u, hd);
+            Real hd[kU];
+            lds_real8(s_hdp + (unsigned)k0 * kRB, hd);
 #pragma unroll
             for (int u = 0; u < kU; ++u) {
-                const double lo = UP ? In[u] : (u ? In[u - 1] : Ic);
-                const double hi = UP ? (u < kU - 1 ? In[u + 1] : Ic) : In[u];
+                const Real lo = UP ? In[u] : (u ? In[u - 1] : Ic);
+                const Real hi = UP ? (u < kU - 1 ? In[u + 1] : Ic) : In[u];
                 x[u] = hd[u] * (lo + hi);
             }
             Ic = UP ? In[0] : In[kU - 1];
@@ -1240,83 +1368,33 @@ __device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, cons
                 unsigned off[kU];
                 lds_u32x8(s_offs + (unsigned)(m * lv.stride + k0 + kstep + 4) * 4u, off);
 #pragma unroll
-                for (int u = 0; u < kU; ++u) raw[u][m] = *(const double *)(src_bytes + (size_t)off[u] * 16u);
+                for (int u = 0; u < kU; ++u) raw[u][m] = *(const Real *)(src_bytes + (size_t)off[u] * 16u);
             }
         } else if (next_src) {
-            prefetch_pass<double, MM>(!UP, Lp, next_src, lv, fd);
+            prefetch_pass<Real, MM>(!UP, Lp, next_src, lv, fd);
         }
         // ---- kVarRedTmem: the previous block's values, transposed, are on their way behind the exp ------
-        uint32_t q0[8], q1[8];
+        RedQ<Real> rq;
         double2 cacc = make_double2(0.0, 0.0);
         if constexpr (RT) {
-            red_fetch(ra.scratch, q0, q1);
+            red_fetch(ra.scratch, rq);
             cacc = red_slot_load(slot);
         }
 
-        // ---- exp of the block's eight layers, with the previous block's shuffle reduction in between ----
-        double t[kU];
+        // ---- exp of the block's eight layers (with the previous block's shuffle lane sum in between) ----
+        Real t[kU];
         constexpr bool RED = (V & kAblReduce) == 0 && !RT;
-        {
-        double tn[kU], r[kU], r2[kU], p[kU], Tj[kU];
-        int nn[kU];
-#pragma unroll
-        for (int u = 0; u < kU; ++u) {
-            int hi = __double2hiint(x[u]);
-            asm("min.s32 %0, %0, 0x40862000;" : "+r"(hi));            // thickness clamp (clamp_thickness), in place
-            x[u] = __hiloint2double(hi, __double2loint(x[u]));
-            tn[u] = fma(-x[u], kK, kMagic);
-        }
-        constexpr bool XP = (V & kAblExp) == 0;
         if constexpr (!RED && !RT) c1 = ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
-        if constexpr (RED)
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {                                    // reduction step 1 (xor 16)
-            const double keep = h4 ? v[i + 4] : v[i], send = h4 ? v[i] : v[i + 4];
-            a4[i] = keep + __shfl_xor_sync(full, send, 16);
-        }
-        if constexpr (XP)
-#pragma unroll
-        for (int u = 0; u < kU; ++u) {
-            nn[u] = __double2loint(tn[u]);
-            tn[u] -= kMagic;
-            Tj[u] = xl_scale(xl_lookup(nn[u], xaux.saddr), nn[u]);       // 2^(j/512) 2^n
-        }
-        if constexpr (XP)
-#pragma unroll
-        for (int u = 0; u < kU; ++u) r[u] = fma(tn[u], kC, -x[u]);
-        if constexpr (RED)
-#pragma unroll
-        for (int i = 0; i < 2; ++i) {                                    // step 2 (xor 8)
-            const double keep = h3 ? a4[i + 2] : a4[i], send = h3 ? a4[i] : a4[i + 2];
-            a2[i] = keep + __shfl_xor_sync(full, send, 8);
-        }
-        if constexpr (XP)
-#pragma unroll
-        for (int u = 0; u < kU; ++u) {
-            r2[u] = r[u] * r[u];
-            p[u] = fma(r[u], 1.0 / 6.0, 0.5);
-        }
-        if constexpr (RED) {                                             // step 3 (xor 4)
-            const double keep = h2 ? a2[1] : a2[0], send = h2 ? a2[0] : a2[1];
-            c1 = keep + __shfl_xor_sync(full, send, 4);
-        }
-        if constexpr (XP)
-#pragma unroll
-        for (int u = 0; u < kU; ++u) p[u] = fma(r2[u], p[u], r[u]);
-        if constexpr (RED) c1 += __shfl_xor_sync(full, c1, 2);           // step 4
-#pragma unroll
-        for (int u = 0; u < kU; ++u) t[u] = XP ? fma(Tj[u], p[u], Tj[u]) : tn[u];
-        if constexpr (RED) c1 += __shfl_xor_sync(full, c1, 1);           // step 5
-        }
+        direct_exp<V, RED>(x, t, xaux, lane, v, c1);
 
-        // ---- both recurrences in sweep order; the block's values for the next iteration's reduction ---
-        double tR[kU];
+        // ---- both recurrences in sweep order; the block's values for the next iteration's lane sum ------
+        Real tR[kU];
         if constexpr (RT)
-            tmem::wait_ld_three(tRw, q0, q1);
+            red_wait(tRw, rq);
         else if constexpr ((V & kAblTstore) == 0)
             tmem::wait_ld<NW>(tRw);
         tmem::unpack<kU>(tRw, tR);
-        if constexpr (RT) red_accumulate(q0, q1, cacc, slot);
+        if constexpr (RT) red_accumulate(rq, cacc, slot);
 #pragma unroll
         for (int o = 0; o < kU; ++o) {
             const int u = UP ? kU - 1 - o : o;
@@ -1324,25 +1402,24 @@ __device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, cons
             ER *= tR[u];
             v[u] = EF + ER;
         }
-        if constexpr ((V & kAblTstore) == 0) tm_store_block<SMALL>(tst.taddr + (uint32_t)(k0 * 2), t);
-        if (acc_on) bacc[kprev + ridx] = bold + c1;
+        if constexpr ((V & kAblTstore) == 0) tm_store_block<SMALL>(tst.taddr + (uint32_t)(k0 * WPR), t);
+        if (acc_on) bacc[kprev + ridx] = bold + (double)c1;
         kprev = k0;
         if constexpr (RT) {
             red_park<SMALL>(v, ra.scratch);
             slot = cbase + k0 * 64;
         }
     }
-
     // ---- lane sum of the last block -------------------------------------------------------------------
     if constexpr (RT) {
-        uint32_t q0[8], q1[8];
-        red_fetch(ra.scratch, q0, q1);              // its wait::st also covers the t-store: the next pass reads it back
+        RedQ<Real> rq;
+        red_fetch(ra.scratch, rq);                  // its wait::st also covers the t-store: the next pass reads it back
         const double2 cacc = red_slot_load(slot);
-        tmem::wait_ld_pair(q0, q1);
-        red_accumulate(q0, q1, cacc, slot);
+        red_wait(rq);
+        red_accumulate(rq, cacc, slot);
     } else {
-        const double c = reduce8<double>(v, lane);
-        if (rlane && kprev + ridx < nl) bacc[kprev + ridx] += c;
+        const Real c = reduce8<Real>(v, lane);
+        if (rlane && kprev + ridx < nl) bacc[kprev + ridx] += (double)c;
         tmem::wait_st();
     }
 }
@@ -1363,17 +1440,17 @@ __device__ __forceinline__ void dispatch_pass(const bool lw, const bool up, cons
         else
             sweep_pass<Real, MM, true, false, FRESH, V>(lane, nl, Lp, wF, wR, bs, src_lane, next_src, fd, lv, tst, dn, coef, coef + Lp, tabT);
     } else {
-        if constexpr (FRESH && MM > 0 && sizeof(Real) == 8 && (V & kVarSwDirect) != 0) {
+        if constexpr (FRESH && MM > 0 && (V & kVarSwDirect) != 0) {
             if (up)
-                sw_fresh_pass<MM, true, V>(lane, nl, Lp, wF, wR, bg, src_lane, next_src, fd, lv, tst, bacc_up, tabT, ra);
+                sw_fresh_pass<Real, MM, true, V>(lane, nl, Lp, wF, wR, bg, src_lane, next_src, fd, lv, tst, bacc_up, tabT, ra);
             else
-                sw_fresh_pass<MM, false, V>(lane, nl, Lp, wF, wR, bs, src_lane, next_src, fd, lv, tst, dn, tabT, ra);
-        } else if constexpr (!FRESH && MM > 0 && sizeof(Real) == 8 && (V & kVarSwDirect) != 0 && (V & kVarRedTmem) != 0) {
+                sw_fresh_pass<Real, MM, false, V>(lane, nl, Lp, wF, wR, bs, src_lane, next_src, fd, lv, tst, dn, tabT, ra);
+        } else if constexpr (!FRESH && MM > 0 && (V & kVarSwDirect) != 0 && (V & kVarRedTmem) != 0) {
             if (next_src) prefetch_pass<Real, MM>(!up, Lp, next_src, lv, fd);
             if (up)
-                sw_replay_pass<true, (V & kVarSmallSt) != 0>(Lp, (double)wR, (double)bg, *reinterpret_cast<const TStore<double> *>(&tst), ra);
+                sw_replay_pass<Real, true, (V & kVarSmallSt) != 0>(Lp, wR, bg, tst, ra);
             else
-                sw_replay_pass<false, (V & kVarSmallSt) != 0>(Lp, (double)wR, (double)bs, *reinterpret_cast<const TStore<double> *>(&tst), ra);
+                sw_replay_pass<Real, false, (V & kVarSmallSt) != 0>(Lp, wR, bs, tst, ra);
         } else if (up)
             sweep_pass<Real, MM, false, true, FRESH, V>(lane, nl, Lp, wF, wR, bg, src_lane, next_src, fd, lv, tst, bacc_up, coef, coef, tabT);
         else
@@ -1385,7 +1462,7 @@ __device__ __forceinline__ void dispatch_pass(const bool lw, const bool up, cons
 // live in registers); MM = 0 selects the resident-tau path.  Persistent CTAs: task = (column, c)
 // with c < ctas_per_col; warp w of the CTA sweeps part c * W + w of the column.
 template <typename Real, int MM, int V = 0>
-__global__ void __launch_bounds__(variant_threads(V), 1) flux_kernel(const FluxArgs<Real> a) {
+__global__ void __launch_bounds__(variant_threads<Real>(V), 1) flux_kernel(const FluxArgs<Real> a) {
     constexpr bool FUSED = MM > 0;
     constexpr int MR = MM > 0 ? MM : 1;
     constexpr bool TM = (V & kVarTmem) != 0, CS = (V & kVarCoefSmem) != 0, PA = (V & kVarPartial) != 0;
@@ -1408,8 +1485,8 @@ __global__ void __launch_bounds__(variant_threads(V), 1) flux_kernel(const FluxA
     constexpr unsigned kXlWindow = xl_window(V);
     const unsigned smem_window0 = (unsigned)__cvta_generic_to_shared(smem_raw);      // shared-window address of smem_raw
     // staged coefficient rows (kVarCoefSmem): in the warp's region, or (kVarRedTmem) above the exp table
-    Real *cw = RT ? (Real *)(smem_raw + (kXlWindow + kXlBytes - smem_window0) + (size_t)warp * lay.coef_bytes)
-                  : (Real *)(wbase + lay.warp_coef);
+    Real *cw = (RT && sizeof(Real) == 8) ? (Real *)(smem_raw + (kXlWindow + kXlBytes - smem_window0) + (size_t)warp * lay.coef_bytes)
+                                         : (Real *)(wbase + lay.warp_coef);
     Real *ts = (Real *)(wbase + lay.warp_ts);
     double *sacc = (double *)(smem_raw + lay.shared_total + lay.warp_bacc);   // warp 0's accumulators, free in the epilogue
     Real *coef_cta = a.coefbuf + (size_t)blockIdx.x * a.B * 4 * Lp;
@@ -1422,9 +1499,9 @@ __global__ void __launch_bounds__(variant_threads(V), 1) flux_kernel(const FluxA
     TStore<Real> tst{ts + lane, 0u, a.tm_rows};
     // exp tables: this lane's entry of the 2^(j/32) table (kVarExpTable); the replicated 2^(j/512) table (kVarExpLds)
     double *xtab = (double *)(smem_raw + lay.off_xtab);
-    if constexpr ((V & kVarSwDirect) != 0)      // the table sits at shared-window address kXlWindow (launch_flux sizes the window)
+    if constexpr ((V & kVarSwDirect) != 0 && sizeof(Real) == 8)      // the table sits at shared-window address kXlWindow (launch_flux sizes the window)
         xtab = (double *)(smem_raw + (kXlWindow - smem_window0));
-    if constexpr ((V & (kVarExpLds | kVarSwDirect)) != 0)
+    if constexpr ((V & (kVarExpLds | kVarSwDirect)) != 0 && sizeof(Real) == 8)
         for (int i = tid; i < kXlN * kXlCopies; i += nthr) xtab[i] = a.exp_tab[i / kXlCopies];
     const ExpAux tabT{kExpTab[lane], xtab + (lane & (kXlCopies - 1)), kXlWindow | ((unsigned)(lane & (kXlCopies - 1)) << 3)};
     // kVarRedTmem: this warp's class accumulators [2][Lp / kU][4][8] double2 and its 16 exchange columns in tensor memory
@@ -1640,20 +1717,23 @@ __global__ void __launch_bounds__(variant_threads(V), 1) flux_kernel(const FluxA
             } else if constexpr (RT) {
                 // class accumulators of the short-wave passes: indexed by layer; an upward layer k is interface k
                 // (padding layers >= nl hold junk), a downward layer k interface k + 1.  Slot of layer k, class c:
-                // (k / 8) * 32 + (k & 3) + 4 c, .x for k % 8 < 4, .y otherwise; classes added in order.
+                // FP64 (k / 8) * 32 + (k & 3) + 4 c, .x for k % 8 < 4, .y otherwise; FP32 (k / 8) * 32 + (k % 8) / 2 + 4 c,
+                // .x for even k; classes added in order.
+                auto pslot = [](int k) { return (k >> 3) * 32 + (sizeof(Real) == 8 ? (k & 3) : ((k & 7) >> 1)); };
+                auto phigh = [](int k) { return sizeof(Real) == 8 ? (k & 4) != 0 : (k & 1) != 0; };
                 for (int i = lane; i < L; i += 32) {
                     double su = bacc_up[i], sd = bacc_dn[i];
                     if (!lw) {
                         if (i < nl) {
-                            const double2 *pu = pacc + (i >> 3) * 32 + (i & 3);
+                            const double2 *pu = pacc + pslot(i);
 #pragma unroll
-                            for (int c = 0; c < 8; ++c) su += (i & 4) ? pu[4 * c].y : pu[4 * c].x;
+                            for (int c = 0; c < 8; ++c) su += phigh(i) ? pu[4 * c].y : pu[4 * c].x;
                         }
                         if (i >= 1) {
                             const int k = i - 1;
-                            const double2 *pd = pacc + Lp * 4 + (k >> 3) * 32 + (k & 3);
+                            const double2 *pd = pacc + Lp * 4 + pslot(k);
 #pragma unroll
-                            for (int c = 0; c < 8; ++c) sd += (k & 4) ? pd[4 * c].y : pd[4 * c].x;
+                            for (int c = 0; c < 8; ++c) sd += phigh(k) ? pd[4 * c].y : pd[4 * c].x;
                         }
                     }
                     o[i] = su;

@@ -91,6 +91,9 @@ __device__ __forceinline__ void ld_small(uint32_t addr, uint32_t (&r)[NW]) {
         asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0, %1}, [%2];" : "=r"(r[0]), "=r"(r[1]) : "r"(addr));
     }
 }
+__device__ __forceinline__ void st_one(uint32_t addr, uint32_t r) {      // one column per lane (an FP32 value)
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x1.b32 [%0], {%1};" ::"r"(addr), "r"(r) : "memory");
+}
 template <int NW>
 __device__ __forceinline__ void st_small(uint32_t addr, const uint32_t (&r)[NW]) {
     static_assert(NW == 2 || NW == 4, "2 or 4 columns");
@@ -128,6 +131,26 @@ __device__ __forceinline__ void ld_16x256b_x2(uint32_t addr, uint32_t (&r)[8]) {
     asm volatile("tcgen05.ld.sync.aligned.16x256b.x2.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
                  : "r"(addr));
+}
+// The same shape over 8 columns (.x1): columns 2 (t % 4), 2 (t % 4) + 1 of lanes t / 4 (r[0], r[1]) and t / 4 + 8
+// (r[2], r[3]) -- FP32 values 2 (t % 4) and 2 (t % 4) + 1 of those lanes when 8 values were parked per lane.
+__device__ __forceinline__ void ld_16x256b_x1(uint32_t addr, uint32_t (&r)[4]) {
+    asm volatile("tcgen05.ld.sync.aligned.16x256b.x1.b32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+                 : "r"(addr));
+}
+__device__ __forceinline__ void wait_ld_pair(uint32_t (&a)[4], uint32_t (&b)[4]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(a[0]), "+r"(a[1]), "+r"(a[2]), "+r"(a[3]), "+r"(b[0]), "+r"(b[1]), "+r"(b[2]), "+r"(b[3])
+                 :
+                 : "memory");
+}
+__device__ __forceinline__ void wait_ld_three(uint32_t (&r)[8], uint32_t (&a)[4], uint32_t (&b)[4]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                   "+r"(a[0]), "+r"(a[1]), "+r"(a[2]), "+r"(a[3]), "+r"(b[0]), "+r"(b[1]), "+r"(b[2]), "+r"(b[3])
+                 :
+                 : "memory");
 }
 // Wait for every outstanding tcgen05.ld of the thread: two transposed blocks, or those and a block of 16 words.
 __device__ __forceinline__ void wait_ld_pair(uint32_t (&a)[8], uint32_t (&b)[8]) {

@@ -249,8 +249,11 @@ def test_tensor_memory_tstore_equals_shared_memory_tstore(precision, monkeypatch
     long-wave coefficient rows in shared memory; CMB200_FLUX_VARIANT=0 selects the plain kernel
     (t-store in shared memory, coefficients broadcast with shuffles).  Same arithmetic in the same
     order: the results are equal bit for bit, in both optical-depth sources, split and whole-column
-    mode.  Variant 3 is the FP32 default; the FP64 default adds the shared-memory exp table (error
-    <= 1e-14 per layer) and the direct short-wave pass, and has to stay within 1e-12 of them."""
+    mode.  The defaults differ from them in the table-fused path only, by rounding: the direct short-wave
+    passes sum the lanes in another order (through tensor memory), FP64 adds the shared-memory exp table
+    (error <= 1e-14 per layer) and has to stay within 1e-12 of variant 0, FP32 evaluates exp with a bare
+    ex2.approx and has to stay within a few FP32 ulp (4e-6 of the largest flux; heating: the FP32 rounding
+    floor of the flux differences).  On resident tau the FP32 default IS variant 3."""
     c = load_case('two_mol_nz41')
     plan = make_plan(c, precision=precision, tables=True)
     tau = oracle_tau(c)
@@ -269,7 +272,14 @@ def test_tensor_memory_tstore_equals_shared_memory_tstore(precision, monkeypatch
                 assert np.isfinite(b[k]).all() and np.isfinite(d[k]).all()
                 assert np.array_equal(a[k], b[k])
                 if precision == 'f32':
-                    assert np.array_equal(a[k], d[k])
+                    if a is res['0'][1]:                       # resident tau: same kernel
+                        assert np.array_equal(a[k], d[k])
+                    elif k != 'heating':
+                        assert relmax(d[k], a[k]) < 4e-6
+                    else:
+                        for i in range(min(n_col, 16)):
+                            assert heating_ok(d[k][i], a[k][i], d['up'][i], d['down'][i], c['bands']['delta'], c['P'], 1e-5,
+                                              eps=np.finfo(np.float32).eps)
                 elif k != 'heating':
                     assert relmax(d[k], a[k]) < 1e-12
                 else:
