@@ -103,6 +103,7 @@ SIGNATURES = {
     'cmb200_flux_workspace_bytes': (C.c_int, [C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]),
     'cmb200_launch_count': (C.c_int64, []),
     'cmb200_test_exp_neg_host': (C.c_int, [c_double_p, C.c_int64, c_double_p]),
+    'cmb200_test_exp_neg_table_host': (C.c_int, [c_double_p, C.c_int64, c_double_p]),
     'cmb200_measure_peaks': (C.c_int, [C.c_int, c_double_p, c_double_p, c_double_p]),
     'cmb200_measure_peaks2': (C.c_int, [C.c_int, c_double_p, c_double_p, c_double_p]),
 }

@@ -123,37 +123,27 @@ static int ensure_partition(cmb200_plan *p, int64_t n_col, int W, int resident_c
 
 // Warps per CTA of kernel variant V for L interfaces: bounded by shared memory (t-store, accumulators,
 // coefficient rows) and, for the tensor-memory t-store, by the 512 columns of a lane quarter shared
-// by the warps w, w + 4, ...  0 = the variant cannot run this L.  tm_rows = layers of a warp's t-store
-// kept in tensor memory (kVarMixed: as many whole blocks as a third of a lane quarter holds).
+// by the warps w, w + 4, ...  0 = the variant cannot run this L.
 template <typename Real, int MM, int V>
-static int variant_warps(int L, int max_smem, int *tmem_cpw, int *tmem_cols, int *tm_rows) {
+static int variant_warps(int L, int max_smem, int *tmem_cpw, int *tmem_cols) {
     const int Lp = padded_layers(L), wpr = (int)(sizeof(Real) / 4);
-    *tmem_cpw = *tmem_cols = *tm_rows = 0;
-    int ts_rows = -1, most = 8;
+    *tmem_cpw = *tmem_cols = 0;
+    int most = 8;
     if (V & kVarTmem) {
-        int per_quarter;
-        if (V & kVarMixed) {
-            per_quarter = 3;
-            *tm_rows = std::min(Lp, (512 / per_quarter / wpr) / kU * kU);
-            ts_rows = Lp - *tm_rows;
-        } else {
-            per_quarter = std::min(variant_threads<Real>(V) / 128, 512 / (Lp * wpr + ((V & kVarRedTmem) ? 2 * kU : 0)));
-            *tm_rows = Lp;
-        }
+        const int per_quarter = std::min(variant_threads<Real>(V) / 128, 512 / (Lp * wpr + ((V & kVarRedTmem) ? 2 * kU : 0)));
         most = 4 * per_quarter;
-        const int cpw = *tm_rows * wpr;
+        const int cpw = Lp * wpr;
         int cols = 32;
         while (cols < per_quarter * cpw) cols *= 2;
         if ((V & kVarRedTmem) && cols < 512 && cols < per_quarter * (cpw + 2 * kU)) cols *= 2;   // exchange columns
         *tmem_cpw = cpw;
         *tmem_cols = cols;
     }
-    const CtaSmem<Real, MM, V> lay(L, ts_rows);
+    const CtaSmem<Real, MM, V> lay(L);
     int W = (size_t)max_smem > lay.shared_total
                 ? (int)std::min<size_t>(most, ((size_t)max_smem - lay.shared_total) / lay.warp_total)
                 : 0;
     if (V & kVarTmem) W = W / 4 * 4;                     // whole lane quarters
-    if ((V & kVarMixed) && W < 12) W = 0;                // the point of the variant is the twelve warps
     return W;
 }
 
@@ -221,13 +211,13 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     }
     int max_smem = 0;
     CMB_CUDA(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, p->device));
-    int tmem_cpw = 0, tmem_cols = 0, tm_rows = 0;
-    const int W = variant_warps<Real, MM, V>(L, max_smem, &tmem_cpw, &tmem_cols, &tm_rows);
+    int tmem_cpw = 0, tmem_cols = 0;
+    const int W = variant_warps<Real, MM, V>(L, max_smem, &tmem_cpw, &tmem_cols);
     if constexpr (V != 0) {      // the variant has to offer at least the warps of the plain kernel, else that one runs
-        int c0, c1, c2;
-        if (W < variant_warps<Real, MM, 0>(L, max_smem, &c0, &c1, &c2)) return launch_flux<Real, MM, 0>(p, io, Tint, s);
+        int c0, c1;
+        if (W < variant_warps<Real, MM, 0>(L, max_smem, &c0, &c1)) return launch_flux<Real, MM, 0>(p, io, Tint, s);
     }
-    const CtaSmem<Real, MM, V> lay(L, (V & kVarMixed) ? Lp - tm_rows : -1, p->B);
+    const CtaSmem<Real, MM, V> lay(L, -1, p->B);
     if (W < 1) {
         set_error("%d levels need %zu bytes of shared memory per CTA; the device offers %d", L, lay.total(1), max_smem);
         return CMB200_ERR_LIMIT;
@@ -361,7 +351,6 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     }
     a.tmem_cpw = tmem_cpw;
     a.tmem_cols = tmem_cols;
-    a.tm_rows = tm_rows;
     flux_kernel<Real, MM, V><<<(unsigned)grid, W * 32, smem, s>>>(a);
     CMB_LAUNCHED();
     if (debug_timing) {   // per-warp sweep cycles of CTA 0's first column next to what the partition gave each warp
@@ -395,11 +384,30 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     return CMB200_OK;
 }
 
-__global__ void exp_neg_test_kernel(const double *__restrict__ x, int64_t n, double *__restrict__ out, bool table) {
+__global__ void exp_neg_test_kernel(const double *__restrict__ x, int64_t n, double *__restrict__ out) {
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-    const double xi = x[i < n ? i : n - 1];          // whole warps: the table routine shuffles
-    const double r = table ? exp_neg_table(xi, kExpTab[threadIdx.x & 31]) : exp_neg(xi);
-    if (i < n) out[i] = r;
+    if (i < n) out[i] = exp_neg(x[i]);
+}
+// The table routine of the direct short-wave passes (direct_exp), eight values per thread, its table built in the
+// same place of the shared window as the flux kernel builds it.
+__global__ void exp_neg_table_test_kernel(const double *__restrict__ x, int64_t n, double *__restrict__ out,
+                                          const double *__restrict__ exp_tab) {
+    constexpr int V = kVarExpLds | kVarSwDirect;
+    const unsigned window0 = (unsigned)__cvta_generic_to_shared(smem_raw);
+    double *xtab = (double *)(smem_raw + (xl_window(V) - window0));
+    for (int i = threadIdx.x; i < kXlN * kXlCopies; i += blockDim.x) xtab[i] = exp_tab[i / kXlCopies];
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const ExpAux xaux{xtab + (lane & (kXlCopies - 1)), xl_window(V) | ((unsigned)(lane & (kXlCopies - 1)) << 3)};
+    for (int64_t base = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * kU; base < n; base += (int64_t)gridDim.x * blockDim.x * kU) {
+        double xv[kU], t[kU], v[kU], c1 = 0.0;
+#pragma unroll
+        for (int u = 0; u < kU; ++u) xv[u] = x[base + u < n ? base + u : n - 1], v[u] = 0.0;
+        direct_exp<V, false>(xv, t, xaux, lane, v, c1);
+#pragma unroll
+        for (int u = 0; u < kU; ++u)
+            if (base + u < n) out[base + u] = t[u];
+    }
 }
 
 template <typename Real, int MM>
@@ -755,7 +763,25 @@ extern "C" int cmb200_test_exp_neg_host(const double *x, int64_t n, double *out)
     DevBuf<double> dx, dout;
     CMB_CUDA(dx.upload(x, n));
     CMB_CUDA(dout.alloc(n));
-    exp_neg_test_kernel<<<(unsigned)((n + 255) / 256), 256>>>(dx.p, n, dout.p, flux_variant() > 0 && (flux_variant() & kVarExpTable) != 0);
+    exp_neg_test_kernel<<<(unsigned)((n + 255) / 256), 256>>>(dx.p, n, dout.p);
+    CMB_LAUNCHED();
+    CMB_CUDA(cudaMemcpy(out, dout.p, n * sizeof(double), cudaMemcpyDeviceToHost));
+    return CMB200_OK;
+}
+
+extern "C" int cmb200_test_exp_neg_table_host(const double *x, int64_t n, double *out) {
+    CMB_CHECK_ARG(x && out && n >= 0, "bad argument");
+    if (n == 0) return CMB200_OK;
+    DevBuf<double> dx, dout, dtab;
+    CMB_CUDA(dx.upload(x, n));
+    CMB_CUDA(dout.alloc(n));
+    std::vector<double> tab(kXlN);
+    for (int j = 0; j < kXlN; ++j) tab[j] = (double)exp2l((long double)j / kXlN);
+    CMB_CUDA(dtab.upload(tab.data(), tab.size()));
+    constexpr int V = kVarExpLds | kVarSwDirect;
+    const int smem = (int)(xl_window(V) + kXlBytes);
+    CMB_CUDA(cudaFuncSetAttribute(exp_neg_table_test_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    exp_neg_table_test_kernel<<<(unsigned)std::min<int64_t>(1024, (n + 256 * kU - 1) / (256 * kU)), 256, smem>>>(dx.p, n, dout.p, dtab.p);
     CMB_LAUNCHED();
     CMB_CUDA(cudaMemcpy(out, dout.p, n * sizeof(double), cudaMemcpyDeviceToHost));
     return CMB200_OK;

@@ -65,7 +65,6 @@ struct FluxArgs {
     int tmem_cols, tmem_cpw;   // TMEM t-store: columns allocated per CTA, columns per warp (V & kVarTmem)
     const double *exp_tab;     // [kXlN] 2^(j/512), correctly rounded (kVarExpLds)
     int seg_space;             // KL is the segment-space table (column = segment * 32 + lane), pitch its row length
-    int tm_rows;               // layers of a warp's t-store kept in tensor memory (the rest in shared memory)
 };
 
 // Kernel variants (template parameter V, a bit set):
@@ -74,24 +73,11 @@ struct FluxArgs {
 //   kVarCoefSmem  the long-wave emission coefficients of the band a warp is working on are staged in
 //                 its shared memory and read with broadcast 128-bit loads instead of being loaded per
 //                 lane from global memory and broadcast with shuffles;
-//   kVarPartial   the warp reduction of a block stops after two exchange steps and the four-lane
-//                 partial sums are accumulated in shared memory per (interface, lane & 7); the eight
-//                 partials are added when the (warp, band) run is written out.
-//   kVarMixed     (with kVarTmem) twelve warps per CTA instead of eight: three warps share a lane quarter
-//                 of tensor memory, so each keeps the first tm_rows layers of its t-store there and the
-//                 rest in shared memory; the kernel is compiled for 384 threads (168 registers).
-//   kVarExpTable  (FP64) exp(-x) = 2^n 2^(j/32) e^r with a 32-entry table of 2^(j/32) held one entry per
-//                 lane and fetched with two shuffles, |r| <= ln2/64 and a degree-6 polynomial: 11 FP64
-//                 instructions per layer instead of 15;
-//   kVarExpRegs   its constants are pinned in registers (a DFMA with a constant-bank operand issues
-//                 every 2.46 cycles instead of every 2, tools/issue_mix_microbench.cu).
 //   kVarExpLds    (FP64) exp(-x) = 2^n 2^(j/512) e^r with the 512-entry table of 2^(j/512) in shared memory,
 //                 replicated sixteen times so that lane l reads bank pair l & 15 whatever j it needs (no
 //                 conflicts), a one-FMA range reduction and e^r = 1 + r + r^2 (1/2 + r/6): 7 FP64
-//                 instructions per layer instead of 15, error <= 1e-14 where the parity gate is 1e-10;
-//   kVarTmPairs   (with kVarTmem) the t-store moves two layers (four 32-bit words) per LDTM / STTM instead
-//                 of a block of eight: no 16-register operand blocks, so ptxas needs no moves around them.
-constexpr int kVarTmem = 1, kVarCoefSmem = 2, kVarPartial = 4, kVarMixed = 8, kVarExpTable = 16, kVarExpRegs = 32;
+//                 instructions per layer instead of 15, error <= 1.1e-14 where the parity gate is 1e-10;
+constexpr int kVarTmem = 1, kVarCoefSmem = 2;
 //   kVarSwDirect  (FP64, fused) short-wave fresh passes run sw_fresh_pass: every block is finished inside its own
 //                 iteration (stage 1, exp, both recurrences, t-store traffic), only the block's warp reduction
 //                 is carried into the next iteration; implies the shared-memory exp table at shared address
@@ -105,7 +91,7 @@ constexpr int kVarTmem = 1, kVarCoefSmem = 2, kVarPartial = 4, kVarMixed = 8, kV
 //                 (warp, band) run is written out.  Short-wave replay-only passes take the same route (sw_replay_pass).
 //   kVarSmallSt   (with kVarSwDirect) the direct short-wave passes store their blocks to tensor memory with eight
 //                 STTM.x2 (the register pair of each value) instead of one STTM.x16.
-constexpr int kVarExpLds = 1024, kVarTmPairs = 2048, kVarSwDirect = 4096, kVarRedTmem = 8192, kVarSmallSt = 16384;
+constexpr int kVarExpLds = 1024, kVarSwDirect = 4096, kVarRedTmem = 8192, kVarSmallSt = 16384;
 // Class accumulators of kVarRedTmem: [2 directions][Lp / kU blocks][32 lanes] double2 (x: layer u, y: layer u + 4 of the
 // block, u = lane & 3; class c = lane >> 2): every thread owns slot `lane` of every block, so a warp's LDS.128 /
 // STS.128 covers 512 contiguous bytes in lane order (no bank conflicts).
@@ -120,22 +106,16 @@ struct RedAux {
 constexpr unsigned xl_window(int V) { return (V & 8192) ? 0x20000u : 0x10000u; }
 constexpr unsigned kXlBytes = 0x10000u;
 constexpr int kXlN = 512, kXlLog = 9, kXlCopies = 16;       // table entries, log2, replicas
-// Per-warp handles of the exp tables: this lane's entry of the 2^(j/32) register table (kVarExpTable) and
-// the shared-memory table already offset by lane & 15 (kVarExpLds).
+// Per-warp handles of the shared-memory exp table (kVarExpLds): already offset by lane & 15.
 struct ExpAux {
-    double tabT;
     const double *lds;
     unsigned saddr;       // kVarSwDirect: xl_window(V) | (lane & 15) * 8
 };
-// Ablation switches for timing experiments only (results are wrong): skip the table loads after the
-// first block, the exp polynomial, the warp reduction, the t-store traffic.
-constexpr int kAblLoads = 64, kAblExp = 128, kAblReduce = 256, kAblTstore = 512;
-constexpr int kPartialLanes = 8;
-// Threads per CTA the kernel is compiled for: 8 warps, or 12 (168 registers) for kVarMixed and for the FP32 direct
-// passes, whose t-stores are half as wide (three warps per lane quarter of tensor memory instead of two).
+// Threads per CTA the kernel is compiled for: 8 warps, or 12 (168 registers) for the FP32 direct passes, whose
+// t-stores are half as wide (three warps per lane quarter of tensor memory instead of two).
 template <typename Real>
 constexpr int variant_threads(int V) {
-    return ((V & kVarMixed) || (sizeof(Real) == 4 && (V & 8192))) ? 384 : 256;
+    return (sizeof(Real) == 4 && (V & 8192)) ? 384 : 256;
 }
 
 constexpr int kU = 8;          // layers per block of a pass (instruction-level parallelism)
@@ -218,11 +198,10 @@ struct CtaSmem {
         off_bsrc = b;
         if (V & kVarRedTmem) b = up16(b + (size_t)2 * B * sizeof(double));
         shared_total = b;
-        // per warp: band accumulators (bacc_up, bacc_dn [Lp + kU] each, or the partial-sum layout
-        // [2][Lp / 2][kPartialLanes][2]), the staged coefficient rows [4][Lp], the t-store [Lp][32]
+        // per warp: band accumulators (bacc_up, bacc_dn [Lp + kU] each), the staged coefficient rows [4][Lp],
+        // the class accumulators (kVarRedTmem), the t-store [Lp][32] (without kVarTmem)
         warp_bacc = 0;
-        warp_coef = up16((V & kVarPartial) ? (size_t)2 * Lp * kPartialLanes * sizeof(double)
-                                           : (size_t)2 * (Lp + kU) * sizeof(double));
+        warp_coef = up16((size_t)2 * (Lp + kU) * sizeof(double));
         coef_bytes = (V & kVarCoefSmem) ? (size_t)4 * Lp * sizeof(Real) : 0;
         if (V & kVarRedTmem) {      // class accumulators here; FP64: the coefficient rows go above the exp table
             warp_pacc = sizeof(Real) == 8 ? warp_coef : up16(warp_coef + coef_bytes);
@@ -240,9 +219,8 @@ struct CtaSmem {
 // tensor-memory address (lane quarter and first column of the warp).
 template <typename Real>
 struct TStore {
-    Real *lane;        // shared-memory row of layer k: lane + (k - tm_rows) * 32
+    Real *lane;        // shared-memory row of layer k: lane + k * 32
     uint32_t taddr;    // tensor-memory column of layer k: taddr + k * (sizeof(Real) / 4)
-    int tm_rows;       // kVarMixed: layers [0, tm_rows) live in tensor memory, the others in shared memory
 };
 
 // exp(-x) for the layer transmissivity.  FP64: n = rint(-x log2 e), r = -x - n ln2 (two-term
@@ -273,42 +251,6 @@ __device__ __forceinline__ double exp_neg(double x) {
     for (int i = 1; i <= 10; ++i) p = fma(p, r, kExpC[i]);
     p = fma(p, r, kExpC[10]);
     return __hiloint2double(__double2hiint(p) + (n << 20), __double2loint(p));
-}
-// Table variant (kVarExpTable): n' = rint(-x 32/ln2) = 32 n + j, r = -x - n' ln2/32 (two-term, the high
-// part has 37 bits so that n' * hi is exact), e^r - 1 = r + r^2 g(r) with g of degree 4 (truncation
-// 3.5e-18), t = T_j + T_j (r + r^2 g), T_j = 2^(j/32) correctly rounded; < 1 ulp overall.
-// kExpT: [0] 32/ln2, [1] 1.5 * 2^52, [2] -hi, [3] -lo, [4..8] 1/720, 1/120, 1/24, 1/6, 1/2.
-__constant__ double kExpT[9] = {0x1.71547652b82fep+5, 6755399441055744.0, -0x1.62e42fefa0000p-6, -0x1.cf79abc9e3b3ap-45,
-                                1.0 / 720.0, 1.0 / 120.0, 1.0 / 24.0, 1.0 / 6.0, 0.5};
-__constant__ double kExpTab[32] = {
-    0x1.0000000000000p+0, 0x1.059b0d3158574p+0, 0x1.0b5586cf9890fp+0, 0x1.11301d0125b51p+0,
-    0x1.172b83c7d517bp+0, 0x1.1d4873168b9aap+0, 0x1.2387a6e756238p+0, 0x1.29e9df51fdee1p+0,
-    0x1.306fe0a31b715p+0, 0x1.371a7373aa9cbp+0, 0x1.3dea64c123422p+0, 0x1.44e086061892dp+0,
-    0x1.4bfdad5362a27p+0, 0x1.5342b569d4f82p+0, 0x1.5ab07dd485429p+0, 0x1.6247eb03a5585p+0,
-    0x1.6a09e667f3bcdp+0, 0x1.71f75e8ec5f74p+0, 0x1.7a11473eb0187p+0, 0x1.82589994cce13p+0,
-    0x1.8ace5422aa0dbp+0, 0x1.93737b0cdc5e5p+0, 0x1.9c49182a3f090p+0, 0x1.a5503b23e255dp+0,
-    0x1.ae89f995ad3adp+0, 0x1.b7f76f2fb5e47p+0, 0x1.c199bdd85529cp+0, 0x1.cb720dcef9069p+0,
-    0x1.d5818dcfba487p+0, 0x1.dfc97337b9b5fp+0, 0x1.ea4afa2a490dap+0, 0x1.f50765b6e4540p+0};
-__device__ __forceinline__ double shfl_f64(double v, int src) {
-    const int lo = __shfl_sync(0xffffffffu, __double2loint(v), src), hi = __shfl_sync(0xffffffffu, __double2hiint(v), src);
-    return __hiloint2double(hi, lo);
-}
-// All 32 lanes of the warp must call this together; tabT = kExpTab[lane].
-__device__ __forceinline__ double exp_neg_table(double x, double tabT) {
-    x = clamp_thickness(x);
-    double tn = fma(-x, kExpT[0], kExpT[1]);
-    const int np = __double2loint(tn);
-    tn -= kExpT[1];
-    const double Tj = shfl_f64(tabT, np & 31);
-    double r = fma(tn, kExpT[2], -x);
-    r = fma(tn, kExpT[3], r);
-    const double r2 = r * r;
-    double g = fma(kExpT[4], r, kExpT[5]);
-    g = fma(g, r, kExpT[6]);
-    g = fma(g, r, kExpT[7]);
-    g = fma(g, r, kExpT[8]);
-    const double t = fma(Tj, fma(r2, g, r), Tj);
-    return __hiloint2double(__double2hiint(t) + ((np >> 5) << 20), __double2loint(t));
 }
 // The same for kU values at once, written step-by-step across the values so that the kU
 // independent dependency chains are adjacent in program order and the FP64 pipe stays busy.
@@ -434,11 +376,8 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
     constexpr bool FUSED = MM > 0;
     constexpr int MR = MM > 0 ? MM : 1;
     constexpr bool F64 = sizeof(Real) == 8;
-    constexpr bool TM = (V & kVarTmem) != 0, CS = (V & kVarCoefSmem) != 0, PA = (V & kVarPartial) != 0;
-    constexpr bool MIX = TM && (V & kVarMixed) != 0;
-    constexpr bool XT = F64 && (V & kVarExpTable) != 0, XR = XT && (V & kVarExpRegs) != 0;
+    constexpr bool TM = (V & kVarTmem) != 0, CS = (V & kVarCoefSmem) != 0;
     constexpr bool XL = F64 && (V & kVarExpLds) != 0;
-    const double tabT = xaux.tabT;
     constexpr int WPR = sizeof(Real) / 4, NW = kU * WPR;   // 32-bit words per value / per block and lane
     using Src = typename std::conditional<FUSED, Real, double>::type;
     const char *src_bytes = (const char *)src_lane;
@@ -448,59 +387,18 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
     const int ridx = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
     const bool rlane = (lane & 3) == 0;
     const int kfirst = UP ? Lp - kU : 0, kstep = UP ? -kU : kU;
-    Real *const tsl = MIX ? tst.lane - tst.tm_rows * 32 : tst.lane;   // layer k sits at tsl[k * 32]
-    // Tensor-memory modes: one block (kU layers) of the t-store <-> NW words per lane.  kVarMixed:
-    // blocks below tm_rows are in tensor memory, the others in shared memory (warp-uniform branch).
-    constexpr int TG = (V & kVarTmPairs) ? 2 * WPR : 0;     // words per small LDTM / STTM: two layers
-    auto ts_fetch = [&](int k0, uint32_t(&w)[NW]) {
-        if constexpr ((V & kAblTstore) != 0) return;
-        if constexpr (TG != 0) {
-#pragma unroll
-            for (int g = 0; g < NW / TG; ++g) {
-                uint32_t q[TG];
-                tmem::ld_small<TG>(tst.taddr + (uint32_t)(k0 * WPR + g * TG), q);
-#pragma unroll
-                for (int i = 0; i < TG; ++i) w[g * TG + i] = q[i];
-            }
-        } else if (!MIX || k0 < tst.tm_rows) {
-            tmem::ld<NW>(tst.taddr + (uint32_t)(k0 * WPR), w);
-        } else {
-            Real tmp[kU];
-#pragma unroll
-            for (int u = 0; u < kU; ++u) tmp[u] = tsl[(k0 + u) * 32];
-            tmem::pack<kU>(tmp, w);
-        }
-    };
+    Real *const tsl = tst.lane;                            // layer k sits at tsl[k * 32]
+    // Tensor memory: one block (kU layers) of the t-store <-> NW words per lane.
+    auto ts_fetch = [&](int k0, uint32_t(&w)[NW]) { tmem::ld<NW>(tst.taddr + (uint32_t)(k0 * WPR), w); };
     auto ts_park = [&](int k0, const Real(&t)[kU]) {
-        if constexpr ((V & kAblTstore) != 0) return;
-        if constexpr (TG != 0) {
-            uint32_t tw[NW];
-            tmem::pack<kU>(t, tw);
-#pragma unroll
-            for (int g = 0; g < NW / TG; ++g) {
-                uint32_t q[TG];
-#pragma unroll
-                for (int i = 0; i < TG; ++i) q[i] = tw[g * TG + i];
-                tmem::st_small<TG>(tst.taddr + (uint32_t)(k0 * WPR + g * TG), q);
-            }
-        } else if (!MIX || k0 < tst.tm_rows) {
-            uint32_t tw[NW];
-            tmem::pack<kU>(t, tw);
-            tmem::st<NW>(tst.taddr + (uint32_t)(k0 * WPR), tw);
-        } else {
-#pragma unroll
-            for (int u = 0; u < kU; ++u) tsl[(k0 + u) * 32] = t[u];
-        }
+        uint32_t tw[NW];
+        tmem::pack<kU>(t, tw);
+        tmem::st<NW>(tst.taddr + (uint32_t)(k0 * WPR), tw);
     };
 
     // ---- warp reduction of v[0..7], split into five steps for the interleave ----------------------
     Real v[kU], a4[4], a2[2], c1;
     auto C1 = [&]() {
-        if constexpr ((V & kAblReduce) != 0) {
-            a4[0] = v[0] + v[1] + v[2] + v[3] + v[4] + v[5] + v[6] + v[7];
-            a4[1] = a4[2] = a4[3] = a4[0];
-            return;
-        }
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const Real keep = h4 ? v[i + 4] : v[i], send = h4 ? v[i] : v[i + 4];
@@ -508,10 +406,6 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
         }
     };
     auto C2 = [&]() {
-        if constexpr ((V & kAblReduce) != 0) {
-            a2[0] = a2[1] = a4[0];
-            return;
-        }
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
             const Real keep = h3 ? a4[i + 2] : a4[i], send = h3 ? a4[i] : a4[i + 2];
@@ -519,40 +413,18 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
         }
     };
     auto C3 = [&]() {
-        if constexpr ((V & kAblReduce) != 0) {
-            c1 = a2[0];
-        } else if constexpr (!PA) {
-            const Real keep = h2 ? a2[1] : a2[0], send = h2 ? a2[0] : a2[1];
-            c1 = keep + __shfl_xor_sync(full, send, 4);
-        }
+        const Real keep = h2 ? a2[1] : a2[0], send = h2 ? a2[0] : a2[1];
+        c1 = keep + __shfl_xor_sync(full, send, 4);
     };
-    auto C4 = [&]() {
-        if constexpr (!PA && !(V & kAblReduce)) c1 += __shfl_xor_sync(full, c1, 2);
-    };
-    auto C5 = [&]() {
-        if constexpr (!PA && !(V & kAblReduce)) c1 += __shfl_xor_sync(full, c1, 1);
-    };
-    // band accumulator of the reduced block: fetched early so that the read latency is off the tail.
-    // Partial mode: after C2 this lane holds the sums over lanes {l, l^8, l^16, l^24} of the two
-    // layers 4 h4 + 2 h3 + {0, 1} of the block -> one 16-byte slot per (layer pair, lane & 7).
+    auto C4 = [&]() { c1 += __shfl_xor_sync(full, c1, 2); };
+    auto C5 = [&]() { c1 += __shfl_xor_sync(full, c1, 1); };
+    // band accumulator of the reduced block: fetched early so that the read latency is off the tail
     double bold = 0.0;
-    double2 bold2 = make_double2(0.0, 0.0);
-    double2 *const pacc = reinterpret_cast<double2 *>(bacc) + (((lane >> 4) & 1) * 2 + ((lane >> 3) & 1)) * kPartialLanes + (lane & 7);
     auto Cload = [&](int kc) {
-        if constexpr (PA) {
-            bold2 = pacc[(kc >> 1) * kPartialLanes];
-        } else {
-            if (rlane && kc + ridx < nl) bold = bacc[kc + ridx];
-        }
+        if (rlane && kc + ridx < nl) bold = bacc[kc + ridx];
     };
     auto Cstore = [&](int kc) {
-        if constexpr (PA) {
-            bold2.x += (double)a2[0];
-            bold2.y += (double)a2[1];
-            pacc[(kc >> 1) * kPartialLanes] = bold2;
-        } else {
-            if (rlane && kc + ridx < nl) bacc[kc + ridx] = bold + (double)c1;
-        }
+        if (rlane && kc + ridx < nl) bacc[kc + ridx] = bold + (double)c1;
     };
 
     // ---- recurrence step of layer kb+u for both chains (stage B) --------------------------------------
@@ -621,16 +493,6 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
                 ldpair(knext, pi - 2, pi & 1 ? cB : cA);
         }
     };
-
-    // constants of the table exp: constant-bank operands, or pinned in registers (kVarExpRegs)
-    double xc[9];
-    if constexpr (XT) {
-#pragma unroll
-        for (int i = 0; i < 9; ++i) {
-            xc[i] = kExpT[i];
-            if constexpr (XR) asm volatile("mov.b64 %0, %0;" : "+d"(xc[i]));
-        }
-    }
 
     if constexpr (FRESH) {
         // raw[u][m]: table value (or tau) of the block's loaded interfaces, fetched one block ahead so
@@ -704,8 +566,7 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
 #pragma unroll
                     for (int u = 0; u < kU; ++u) In[u] = raw[u][0];
                 }
-                if constexpr (!(V & kAblLoads))
-                    if (UP ? k0 >= kU : k0 + kU < Lp) load_block(k0 + kstep);
+                if (UP ? k0 >= kU : k0 + kU < Lp) load_block(k0 + kstep);
                 Real hd[kU];
                 if (FUSED) lds_block(lv.hdp + k0, hd);
 #pragma unroll
@@ -716,69 +577,7 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
                 }
                 Ic = UP ? In[0] : In[kU - 1];
             }
-            if constexpr (XT) {
-                // exp(-x) with the 2^(j/32) table (exp_neg_table), step by step across the block's layers
-                double tn[kU], r[kU], r2[kU], g[kU], Tj[kU];
-                int nsh[kU];
-                if (DO_A) {
-#pragma unroll
-                    for (int u = 0; u < kU; ++u) {
-                        x[u] = clamp_thickness(x[u]);
-                        tn[u] = fma(-x[u], xc[0], xc[1]);
-                    }
-                }
-                if (DO_B) { Bpair(kb, 0, v, knext); park(kb, 0); park(kb, 1); }
-                if (DO_A) {
-#pragma unroll
-                    for (int u = 0; u < kU; ++u) {
-                        const int np = __double2loint(tn[u]);
-                        tn[u] -= xc[1];
-                        nsh[u] = (np >> 5) << 20;
-                        Tj[u] = shfl_f64(tabT, np & 31);
-                    }
-                }
-                if (DO_B) { Bpair(kb, 1, v, knext); park(kb, 2); park(kb, 3); }
-                if (DO_A) {
-#pragma unroll
-                    for (int u = 0; u < kU; ++u) r[u] = fma(tn[u], xc[2], -x[u]);
-                }
-                if (DO_B) { Bpair(kb, 2, v, knext); park(kb, 4); park(kb, 5); }
-                if (DO_A) {
-#pragma unroll
-                    for (int u = 0; u < kU; ++u) r[u] = fma(tn[u], xc[3], r[u]);
-                }
-                // The reduction of block kb is a chain of five shuffle + add steps (~35 cycles each): it starts
-                // right after the block's last recurrence and its last step waits until the end of the iteration.
-                if (DO_B) { Bpair(kb, 3, v, knext); park(kb, 6); park(kb, 7); C1(); }
-                if (DO_A) fetch_replay(k0);
-                if (DO_A) {
-#pragma unroll
-                    for (int u = 0; u < kU; ++u) {
-                        r2[u] = r[u] * r[u];
-                        g[u] = fma(xc[4], r[u], xc[5]);
-                    }
-#pragma unroll
-                    for (int u = 0; u < kU; ++u) g[u] = fma(g[u], r[u], xc[6]);
-                }
-                if (DO_B) C2();
-                if (DO_A) {
-#pragma unroll
-                    for (int u = 0; u < kU; ++u) g[u] = fma(g[u], r[u], xc[7]);
-#pragma unroll
-                    for (int u = 0; u < kU; ++u) g[u] = fma(g[u], r[u], xc[8]);
-                }
-                if (DO_B) C3();
-                if (DO_A) {
-#pragma unroll
-                    for (int u = 0; u < kU; ++u) g[u] = fma(r2[u], g[u], r[u]);
-#pragma unroll
-                    for (int u = 0; u < kU; ++u) {
-                        const double tt = fma(Tj[u], g[u], Tj[u]);
-                        t[u] = __hiloint2double(__double2hiint(tt) + nsh[u], __double2loint(tt));
-                    }
-                }
-                if (DO_B) C4();
-            } else if constexpr (XL) {
+            if constexpr (XL) {
                 // exp(-x) with the shared-memory 2^(j/512) table: n' = rint(-x 512/ln2) = 512 n + j,
                 // r = -x - n' ln2/512 (one FMA with the rounded constant: error <= n' 2^-63, below 1e-13
                 // for every x <= 708), t = 2^n T_j (1 + r + r^2 (1/2 + r/6)); step by step across the layers
@@ -864,7 +663,7 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
                 if (DO_A) fetch_replay(k0);
 #pragma unroll
                 for (int i = 1; i <= 10; ++i) {
-                    if (DO_A && !(V & kAblExp)) {
+                    if (DO_A) {
 #pragma unroll
                         for (int u = 0; u < kU; ++u) p[u] = fma(p[u], r[u], kExpC[i]);
                     }
@@ -899,7 +698,7 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
                 if (DO_A) fetch_replay(k0);
                 if (DO_B) { C1(); C2(); C3(); C4(); C5(); }
             }
-            if (DO_B && !XT) Cstore(kb);
+            if (DO_B) Cstore(kb);
             if (DO_A) {
                 if constexpr (TM) {
                     tmem::wait_ld<NW>(tRw);
@@ -913,10 +712,6 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
                     ldpair(k0, 0, cA);
                     ldpair(k0, 1, cB);
                 }
-            }
-            if (DO_B && XT) {
-                C5();
-                Cstore(kb);
             }
         };
         iter(std::true_type{}, std::false_type{}, kfirst);
@@ -1220,6 +1015,8 @@ __device__ __forceinline__ void lds_u32x8(unsigned off, unsigned (&o)[kU]) {
 // exp(-x) of a block for the direct pass.  FP64: the shared-memory table routine (see the variant list), eight
 // evaluations step by step; with RED the five shuffle stages of the previous block's lane sum are issued in between.
 // FP32: ex2.approx, as everywhere in FP32 mode.
+// (Every `if constexpr` around a `#pragma unroll` loop is braced: unbraced, the discarded statement of a false condition
+// was the pragma, not the loop, and with nvcc 12.9 the pass came back with its arithmetic folded to NaN.)
 template <int V, bool RED>
 __device__ __forceinline__ void direct_exp(double (&x)[kU], double (&t)[kU], const ExpAux xaux, const int lane,
                                            const double (&v)[kU], double &c1) {
@@ -1236,30 +1033,28 @@ __device__ __forceinline__ void direct_exp(double (&x)[kU], double (&t)[kU], con
         x[u] = __hiloint2double(hi, __double2loint(x[u]));
         tn[u] = fma(-x[u], kK, kMagic);
     }
-    constexpr bool XP = (V & kAblExp) == 0;
-    if constexpr (RED)
+    if constexpr (RED) {                                             // reduction step 1 (xor 16)
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {                                    // reduction step 1 (xor 16)
-        const double keep = h4 ? v[i + 4] : v[i], send = h4 ? v[i] : v[i + 4];
-        a4[i] = keep + __shfl_xor_sync(full, send, 16);
+        for (int i = 0; i < 4; ++i) {
+            const double keep = h4 ? v[i + 4] : v[i], send = h4 ? v[i] : v[i + 4];
+            a4[i] = keep + __shfl_xor_sync(full, send, 16);
+        }
     }
-    if constexpr (XP)
 #pragma unroll
     for (int u = 0; u < kU; ++u) {
         nn[u] = __double2loint(tn[u]);
         tn[u] -= kMagic;
         Tj[u] = xl_scale(xl_lookup(nn[u], xaux.saddr), nn[u]);       // 2^(j/512) 2^n
     }
-    if constexpr (XP)
 #pragma unroll
     for (int u = 0; u < kU; ++u) r[u] = fma(tn[u], kC, -x[u]);
-    if constexpr (RED)
+    if constexpr (RED) {                                             // step 2 (xor 8)
 #pragma unroll
-    for (int i = 0; i < 2; ++i) {                                    // step 2 (xor 8)
-        const double keep = h3 ? a4[i + 2] : a4[i], send = h3 ? a4[i] : a4[i + 2];
-        a2[i] = keep + __shfl_xor_sync(full, send, 8);
+        for (int i = 0; i < 2; ++i) {
+            const double keep = h3 ? a4[i + 2] : a4[i], send = h3 ? a4[i] : a4[i + 2];
+            a2[i] = keep + __shfl_xor_sync(full, send, 8);
+        }
     }
-    if constexpr (XP)
 #pragma unroll
     for (int u = 0; u < kU; ++u) {
         r2[u] = r[u] * r[u];
@@ -1269,12 +1064,11 @@ __device__ __forceinline__ void direct_exp(double (&x)[kU], double (&t)[kU], con
         const double keep = h2 ? a2[1] : a2[0], send = h2 ? a2[0] : a2[1];
         c1 = keep + __shfl_xor_sync(full, send, 4);
     }
-    if constexpr (XP)
 #pragma unroll
     for (int u = 0; u < kU; ++u) p[u] = fma(r2[u], p[u], r[u]);
     if constexpr (RED) c1 += __shfl_xor_sync(full, c1, 2);           // step 4
 #pragma unroll
-    for (int u = 0; u < kU; ++u) t[u] = XP ? fma(Tj[u], p[u], Tj[u]) : tn[u];
+    for (int u = 0; u < kU; ++u) t[u] = fma(Tj[u], p[u], Tj[u]);
     if constexpr (RED) c1 += __shfl_xor_sync(full, c1, 1);           // step 5
 }
 template <int V, bool RED>
@@ -1320,18 +1114,12 @@ __device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, cons
     if constexpr (RT) red_park<SMALL>(v, ra.scratch);
 
     // (Tried and dropped: a second buffer of table values, i.e. loads issued two blocks ahead, the loop unrolled by
-    // two -- 9 % slower, profiles/r02_flux_variants_ab.json.  nvcc 12.9 note: the same body written as a lambda
-    // taking the buffer by reference came back with its arithmetic folded to NaN.)
+    // two -- 9 % slower.)
     for (int it = 0, k0 = kfirst; it < nb; ++it, k0 += kstep) {
         auto &raw = fd.raw;
         // replay chain's t of this block
         uint32_t tRw[NW];
-        if constexpr ((V & kAblTstore) == 0) {
-            tmem::ld<NW>(tst.taddr + (uint32_t)(k0 * WPR), tRw);
-        } else {
-#pragma unroll
-            for (int i = 0; i < NW; ++i) tRw[i] = WPR == 2 ? 0x3ff00000u * (i & 1) : 0x3f800000u;
-        }
+        tmem::ld<NW>(tst.taddr + (uint32_t)(k0 * WPR), tRw);
         // band accumulator of the block being reduced (read early, written at the end)
         double bold = 0.0;
         const bool acc_on = !RT && rlane && kprev >= 0 && kprev + ridx < nl;
@@ -1361,8 +1149,7 @@ __device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, cons
             Ic = UP ? In[0] : In[kU - 1];
         }
         // ---- the next block's table values (or the next pass's first block) into the same registers ----
-        if constexpr ((V & kAblLoads) != 0) {
-        } else if (it + 1 < nb) {
+        if (it + 1 < nb) {
 #pragma unroll
             for (int m = 0; m < MM; ++m) {
                 unsigned off[kU];
@@ -1383,15 +1170,14 @@ __device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, cons
 
         // ---- exp of the block's eight layers (with the previous block's shuffle lane sum in between) ----
         Real t[kU];
-        constexpr bool RED = (V & kAblReduce) == 0 && !RT;
-        if constexpr (!RED && !RT) c1 = ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
+        constexpr bool RED = !RT;
         direct_exp<V, RED>(x, t, xaux, lane, v, c1);
 
         // ---- both recurrences in sweep order; the block's values for the next iteration's lane sum ------
         Real tR[kU];
         if constexpr (RT)
             red_wait(tRw, rq);
-        else if constexpr ((V & kAblTstore) == 0)
+        else
             tmem::wait_ld<NW>(tRw);
         tmem::unpack<kU>(tRw, tR);
         if constexpr (RT) red_accumulate(rq, cacc, slot);
@@ -1402,7 +1188,7 @@ __device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, cons
             ER *= tR[u];
             v[u] = EF + ER;
         }
-        if constexpr ((V & kAblTstore) == 0) tm_store_block<SMALL>(tst.taddr + (uint32_t)(k0 * WPR), t);
+        tm_store_block<SMALL>(tst.taddr + (uint32_t)(k0 * WPR), t);
         if (acc_on) bacc[kprev + ridx] = bold + (double)c1;
         kprev = k0;
         if constexpr (RT) {
@@ -1429,22 +1215,21 @@ __device__ __forceinline__ void dispatch_pass(const bool lw, const bool up, cons
                                               const Real wF, const Real wR, const Real bs, const Real bg,
                                               const void *src_lane, const void *next_src, PassFeed<Real, MM> &fd,
                                               const LevelView<Real> &lv, const TStore<Real> tst, double *bacc_up, double *bacc_dn,
-                                              const Real *coef, const ExpAux tabT, const RedAux ra) {
+                                              const Real *coef, const ExpAux xaux, const RedAux ra) {
     // coefficient rows of a band: [0] dn_last, [1] dn_gen, [2] up_first, [3] up_gen.  The value of layer k
-    // of a downward pass belongs to interface k + 1: the plain accumulators are indexed by interface, the
-    // partial-sum accumulators (kVarPartial) by layer.
-    double *const dn = (V & kVarPartial) ? bacc_dn : bacc_dn + 1;
+    // of a downward pass belongs to interface k + 1 (the plain accumulators are indexed by interface).
+    double *const dn = bacc_dn + 1;
     if (lw) {
         if (up)
-            sweep_pass<Real, MM, true, true, FRESH, V>(lane, nl, Lp, wF, wR, bg, src_lane, next_src, fd, lv, tst, bacc_up, coef + 2 * Lp, coef + 3 * Lp, tabT);
+            sweep_pass<Real, MM, true, true, FRESH, V>(lane, nl, Lp, wF, wR, bg, src_lane, next_src, fd, lv, tst, bacc_up, coef + 2 * Lp, coef + 3 * Lp, xaux);
         else
-            sweep_pass<Real, MM, true, false, FRESH, V>(lane, nl, Lp, wF, wR, bs, src_lane, next_src, fd, lv, tst, dn, coef, coef + Lp, tabT);
+            sweep_pass<Real, MM, true, false, FRESH, V>(lane, nl, Lp, wF, wR, bs, src_lane, next_src, fd, lv, tst, dn, coef, coef + Lp, xaux);
     } else {
         if constexpr (FRESH && MM > 0 && (V & kVarSwDirect) != 0) {
             if (up)
-                sw_fresh_pass<Real, MM, true, V>(lane, nl, Lp, wF, wR, bg, src_lane, next_src, fd, lv, tst, bacc_up, tabT, ra);
+                sw_fresh_pass<Real, MM, true, V>(lane, nl, Lp, wF, wR, bg, src_lane, next_src, fd, lv, tst, bacc_up, xaux, ra);
             else
-                sw_fresh_pass<Real, MM, false, V>(lane, nl, Lp, wF, wR, bs, src_lane, next_src, fd, lv, tst, dn, tabT, ra);
+                sw_fresh_pass<Real, MM, false, V>(lane, nl, Lp, wF, wR, bs, src_lane, next_src, fd, lv, tst, dn, xaux, ra);
         } else if constexpr (!FRESH && MM > 0 && (V & kVarSwDirect) != 0 && (V & kVarRedTmem) != 0) {
             if (next_src) prefetch_pass<Real, MM>(!up, Lp, next_src, lv, fd);
             if (up)
@@ -1452,9 +1237,9 @@ __device__ __forceinline__ void dispatch_pass(const bool lw, const bool up, cons
             else
                 sw_replay_pass<Real, false, (V & kVarSmallSt) != 0>(Lp, wR, bs, tst, ra);
         } else if (up)
-            sweep_pass<Real, MM, false, true, FRESH, V>(lane, nl, Lp, wF, wR, bg, src_lane, next_src, fd, lv, tst, bacc_up, coef, coef, tabT);
+            sweep_pass<Real, MM, false, true, FRESH, V>(lane, nl, Lp, wF, wR, bg, src_lane, next_src, fd, lv, tst, bacc_up, coef, coef, xaux);
         else
-            sweep_pass<Real, MM, false, false, FRESH, V>(lane, nl, Lp, wF, wR, bs, src_lane, next_src, fd, lv, tst, dn, coef, coef, tabT);
+            sweep_pass<Real, MM, false, false, FRESH, V>(lane, nl, Lp, wF, wR, bs, src_lane, next_src, fd, lv, tst, dn, coef, coef, xaux);
     }
 }
 
@@ -1465,13 +1250,12 @@ template <typename Real, int MM, int V = 0>
 __global__ void __launch_bounds__(variant_threads<Real>(V), 1) flux_kernel(const FluxArgs<Real> a) {
     constexpr bool FUSED = MM > 0;
     constexpr int MR = MM > 0 ? MM : 1;
-    constexpr bool TM = (V & kVarTmem) != 0, CS = (V & kVarCoefSmem) != 0, PA = (V & kVarPartial) != 0;
+    constexpr bool TM = (V & kVarTmem) != 0, CS = (V & kVarCoefSmem) != 0;
     constexpr int WPR = sizeof(Real) / 4, NW = kU * WPR;
     const int tid = threadIdx.x, nthr = blockDim.x, W = nthr >> 5, warp = tid >> 5, lane = tid & 31;
     const int L = a.L, nl = a.L - 1, Lp = padded_layers(a.L), LS = Lp + kU, C = a.ctas_per_col;
 
-    const int ts_rows = (V & kVarMixed) ? Lp - a.tm_rows : -1;     // t-store layers in shared memory
-    const CtaSmem<Real, MM, V> lay(L, ts_rows, a.B);
+    const CtaSmem<Real, MM, V> lay(L, -1, a.B);
     unsigned *lev_offdn = (unsigned *)(smem_raw + lay.off_offdn);
     unsigned *lev_offup = (unsigned *)(smem_raw + lay.off_offup);
     Real *lev_qg = (Real *)(smem_raw + lay.off_qg);
@@ -1479,8 +1263,8 @@ __global__ void __launch_bounds__(variant_threads<Real>(V), 1) flux_kernel(const
     const int lstride = lay.lev_stride;
     unsigned char *wbase = smem_raw + lay.shared_total + (size_t)warp * lay.warp_total;
     double *bacc_up = (double *)(wbase + lay.warp_bacc);
-    double *bacc_dn = bacc_up + (PA ? Lp * kPartialLanes : LS);
-    const int n_bacc = PA ? 2 * Lp * kPartialLanes : 2 * LS;      // accumulator doubles per warp
+    double *bacc_dn = bacc_up + LS;
+    const int n_bacc = 2 * LS;                                    // accumulator doubles per warp
     constexpr bool RT = (V & kVarRedTmem) != 0;
     constexpr unsigned kXlWindow = xl_window(V);
     const unsigned smem_window0 = (unsigned)__cvta_generic_to_shared(smem_raw);      // shared-window address of smem_raw
@@ -1496,14 +1280,14 @@ __global__ void __launch_bounds__(variant_threads<Real>(V), 1) flux_kernel(const
     for (int i = lane; i < n_bacc; i += 32) bacc_up[i] = 0.0;
     // The t-store: the first replay of a run reads it with weight 0, so it has to hold finite numbers.
     __shared__ uint32_t s_tmem_base;
-    TStore<Real> tst{ts + lane, 0u, a.tm_rows};
-    // exp tables: this lane's entry of the 2^(j/32) table (kVarExpTable); the replicated 2^(j/512) table (kVarExpLds)
+    TStore<Real> tst{ts + lane, 0u};
+    // the replicated 2^(j/512) table (kVarExpLds)
     double *xtab = (double *)(smem_raw + lay.off_xtab);
     if constexpr ((V & kVarSwDirect) != 0 && sizeof(Real) == 8)      // the table sits at shared-window address kXlWindow (launch_flux sizes the window)
         xtab = (double *)(smem_raw + (kXlWindow - smem_window0));
     if constexpr ((V & (kVarExpLds | kVarSwDirect)) != 0 && sizeof(Real) == 8)
         for (int i = tid; i < kXlN * kXlCopies; i += nthr) xtab[i] = a.exp_tab[i / kXlCopies];
-    const ExpAux tabT{kExpTab[lane], xtab + (lane & (kXlCopies - 1)), kXlWindow | ((unsigned)(lane & (kXlCopies - 1)) << 3)};
+    const ExpAux xaux{xtab + (lane & (kXlCopies - 1)), kXlWindow | ((unsigned)(lane & (kXlCopies - 1)) << 3)};
     // kVarRedTmem: this warp's class accumulators [2][Lp / kU][4][8] double2 and its 16 exchange columns in tensor memory
     RedAux ra{0u, 0u, 0u};
     double2 *pacc = nullptr;
@@ -1527,10 +1311,8 @@ __global__ void __launch_bounds__(variant_threads<Real>(V), 1) flux_kernel(const
         uint32_t zero[NW];
 #pragma unroll
         for (int i = 0; i < NW; ++i) zero[i] = 0u;
-        for (int k0 = 0; k0 < a.tm_rows; k0 += kU) tmem::st<NW>(tst.taddr + (uint32_t)(k0 * WPR), zero);
+        for (int k0 = 0; k0 < Lp; k0 += kU) tmem::st<NW>(tst.taddr + (uint32_t)(k0 * WPR), zero);
         tmem::wait_st();
-        if constexpr ((V & kVarMixed) != 0)
-            for (int i = lane; i < ts_rows * 32; i += 32) ts[i] = Real(0);
     } else {
         for (int i = lane; i < Lp * 32; i += 32) ts[i] = Real(0);
     }
@@ -1548,6 +1330,29 @@ __global__ void __launch_bounds__(variant_threads<Real>(V), 1) flux_kernel(const
         const int cpart = (int)(task - col * C);
         const int64_t region = C == 1 ? (int64_t)blockIdx.x : col;
         const long long t_task0 = a.dbg ? clock64() : 0;
+
+        // The inputs of the column this CTA is likely to get next (tasks are handed out in order, so about gridDim.x
+        // further on) are pulled into L2 now: the prologue is a chain of dependent global loads, and from HBM each
+        // link costs three times what it costs from L2.  A wrong guess only wastes a few 128-byte lines.
+        if (C == 1) {
+            const int64_t nc = col + gridDim.x;
+            if (nc < a.n_col) {
+                auto pull = [&](const void *base, int bytes) {
+                    for (int off = tid * 128; off < bytes; off += nthr * 128)
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"((const char *)base + off));
+                };
+                pull(a.T + nc * nl, nl * 8);
+                pull(a.Tint + nc * L, L * 8);
+                pull(a.T_g + nc, 8);
+                if (a.albedo) pull(a.albedo + nc, 8);
+                if (FUSED) {
+                    for (int m = 0; m < MR; ++m) {
+                        pull(a.tidx + ((int64_t)m * a.n_col + nc) * L, L);
+                        if (a.q_col_stride) pull(a.q + m * a.q_mol_stride + nc * a.q_col_stride, L * 8);
+                    }
+                }
+            }
+        }
 
         // ---- the column's level tables ---------------------------------------------------------------
         for (int idx = tid; idx < MR * lstride; idx += nthr) {
@@ -1676,7 +1481,7 @@ __global__ void __launch_bounds__(variant_threads<Real>(V), 1) flux_kernel(const
             const bool first_chain = __ldg(a.seg_c0 + s) == 0;
             const double bnd_up = first_chain ? (double)bg * a.band_sumw[j] : 0.0;
             const double bnd_dn = first_chain ? (double)bs * a.band_sumw[j] : 0.0;
-            if (!PA && first_chain && lane == 0) {
+            if (first_chain && lane == 0) {
                 bacc_up[L - 1] += bnd_up;
                 bacc_dn[0] += bnd_dn;
             }
@@ -1686,35 +1491,17 @@ __global__ void __launch_bounds__(variant_threads<Real>(V), 1) flux_kernel(const
                 const void *src_lane = srcN;
                 if (s + 1 < s1) seg_params(s + 1, wN, srcN);
                 dispatch_pass<Real, MM, true, V>(lw, up, lane, nl, Lp, wF, wR, bs, bg, src_lane, s + 1 < e ? srcN : nullptr, fd, lv,
-                                                 tst, bacc_up, bacc_dn, coef, tabT, ra);
+                                                 tst, bacc_up, bacc_dn, coef, xaux, ra);
                 wR = wF;
                 up = !up;
             }
             dispatch_pass<Real, MM, false, V>(lw, up, lane, nl, Lp, Real(0), wR, bs, bg, nullptr, s < s1 ? srcN : nullptr, fd, lv,
-                                              tst, bacc_up, bacc_dn, coef, tabT, ra);
+                                              tst, bacc_up, bacc_dn, coef, xaux, ra);
             up = !up;
             // ---- partial band sums of this (warp, band) run -> scratch slot ---------------------------
             __syncwarp();
             double *o = a.scratch + ((region * a.n_slots + slot) * 2) * (int64_t)L;
-            if constexpr (PA) {
-                // accumulators [layer / 2][lane & 7][layer % 2]: add the eight partials in order; an upward
-                // layer k is interface k, a downward layer k interface k + 1
-                for (int i = lane; i < L; i += 32) {
-                    double su = i == L - 1 ? bnd_up : 0.0, sd = i == 0 ? bnd_dn : 0.0;
-                    if (i < nl) {
-                        const double *pu = bacc_up + (i >> 1) * (2 * kPartialLanes) + (i & 1);
-#pragma unroll
-                        for (int c = 0; c < kPartialLanes; ++c) su += pu[2 * c];
-                    }
-                    if (i >= 1) {
-                        const double *pd = bacc_dn + ((i - 1) >> 1) * (2 * kPartialLanes) + ((i - 1) & 1);
-#pragma unroll
-                        for (int c = 0; c < kPartialLanes; ++c) sd += pd[2 * c];
-                    }
-                    o[i] = su;
-                    o[L + i] = sd;
-                }
-            } else if constexpr (RT) {
+            if constexpr (RT) {
                 // class accumulators of the short-wave passes: indexed by layer; an upward layer k is interface k
                 // (padding layers >= nl hold junk), a downward layer k interface k + 1.  Slot of layer k, class c:
                 // FP64 (k / 8) * 32 + (k & 3) + 4 c, .x for k % 8 < 4, .y otherwise; FP32 (k / 8) * 32 + (k % 8) / 2 + 4 c,

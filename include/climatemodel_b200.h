@@ -274,8 +274,11 @@ int cmb200_measure_peaks(int device, double *fp64_tflops, double *fp32_tflops, d
  * the flux kernel's table stream.  Any pointer may be NULL. */
 int cmb200_measure_peaks2(int device, double *fp64_reg_tflops, double *fp32_reg_tflops, double *l2_stream_gbs);
 
-/* Test hook: the flux kernel's own exp(-x) routine evaluated on n values (HOST pointers). */
+/* Test hooks: the flux kernel's own exp(-x) routines evaluated on n values (HOST pointers) -- the degree-11
+ * polynomial of the plain and long-wave passes (<= 2 ulp), and the shared-memory table routine of the FP64 default's
+ * short-wave passes (2^(j/512) table + cubic, error <= 1.1e-14 for x <= 40, <= 1e-13 up to the clamp at 708).  Both stand in for np.exp in real_gas.py:159-160. */
 int cmb200_test_exp_neg_host(const double *x, int64_t n, double *out);
+int cmb200_test_exp_neg_table_host(const double *x, int64_t n, double *out);
 
 #ifdef __cplusplus
 }

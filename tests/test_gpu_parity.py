@@ -75,6 +75,25 @@ def test_layer_transmissivity_exp_accuracy():
     assert np.all(out[:4] < 1e-300) and np.all(out[:4] >= 0)
 
 
+def test_layer_transmissivity_table_exp_accuracy():
+    """The shared-memory table routine the FP64 default's short-wave passes use (2^(j/512) table, one-FMA range
+    reduction, cubic): relative error <= 1e-13 up to the clamp at 708 (the one-FMA reduction loses n' 2^-63, n' =
+    x 512/ln2) and <= 1.1e-14 for x <= 40 (cubic truncation r^4 / 24 <= 8.7e-15), where a transmissivity still matters (exp(-40) = 4e-18) -- four orders of
+    magnitude inside the 1e-10 gate, so 99 layers of it stay below 1e-12 -- and ~0 beyond the clamp."""
+    from climatemodel_b200 import _lib
+    rng = np.random.default_rng(1)
+    x = np.concatenate((10 ** rng.uniform(-12, 2.8, 200000), rng.uniform(0, 40, 200000), [0.0, 1e-300, 700.0, 707.5]))
+    out = np.empty_like(x)
+    _lib.check(_lib.load().cmb200_test_exp_neg_table_host(_lib.dptr(x), x.size, _lib.dptr(out)))
+    ref = np.exp(-x)
+    rel = np.abs(out - ref) / ref
+    assert rel.max() < 1e-13
+    assert rel[x <= 40].max() < 1.2e-14
+    big = np.array([709.0, 1e3, 1e6, 1e300])
+    _lib.check(_lib.load().cmb200_test_exp_neg_table_host(_lib.dptr(big), big.size, _lib.dptr(out[:4])))
+    assert np.all(out[:4] < 1e-300) and np.all(out[:4] >= 0)
+
+
 # ---- A3 ------------------------------------------------------------------------------------
 @pytest.mark.parametrize('name', CASES)
 def test_optical_depth_bit_exact(rg, name):
@@ -251,7 +270,7 @@ def test_tensor_memory_tstore_equals_shared_memory_tstore(precision, monkeypatch
     order: the results are equal bit for bit, in both optical-depth sources, split and whole-column
     mode.  The defaults differ from them in the table-fused path only, by rounding: the direct short-wave
     passes sum the lanes in another order (through tensor memory), FP64 adds the shared-memory exp table
-    (error <= 1e-14 per layer) and has to stay within 1e-12 of variant 0, FP32 evaluates exp with a bare
+    (error <= 1.1e-14 per layer) and has to stay within 1e-12 of variant 0, FP32 evaluates exp with a bare
     ex2.approx and has to stay within a few FP32 ulp (4e-6 of the largest flux; heating: the FP32 rounding
     floor of the flux differences).  On resident tau the FP32 default IS variant 3."""
     c = load_case('two_mol_nz41')

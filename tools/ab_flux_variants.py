@@ -1,6 +1,6 @@
 """A/B of the flux kernel variants (CMB200_FLUX_VARIANT, csrc/flux_kernels.cuh) on one GPU.
 
-    python tools/ab_flux_variants.py [--columns 17760] [--variants 0,1,3,7] [--reps 5] [--out file.json]
+    python tools/ab_flux_variants.py [--columns 17760] [--variants 0,3,5123] [--reps 5] [--out file.json]
 
 Same workload shape as bench.py (100 levels x 10.4k bins, 2 molecules, per-column T / q), a
 column count that is a multiple of the SM count; every variant is timed with CUDA events and its
@@ -21,7 +21,7 @@ sys.path.insert(0, ROOT)
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--columns', type=int, default=17760)
-    ap.add_argument('--variants', default='0,1,3,7')
+    ap.add_argument('--variants', default='0,3,5123')
     ap.add_argument('--reps', type=int, default=5)
     ap.add_argument('--out', default=None)
     a = ap.parse_args()
