@@ -367,6 +367,7 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
                 if (j != last) (p->hsw[j] ? r_sw : r_lw)++;
                 last = j;
             }
+            if (w == 0) fprintf(stderr, "cmb200 timing: prologue split: level tables (warp 0) %lld, coefficients (warp 1) %lld, both (warp 2) %lld, level tables (warp 3) %lld\n", h[60], h[61], h[62], h[63]);
             fprintf(stderr, "cmb200 timing: warp %d sweep %lld (prologue %lld, whole task %lld)  fresh sw %d lw %d  runs sw %d lw %d\n", w, h[w], h[32 + w], h[48 + w], n_sw, n_lw, r_sw, r_lw);
         }
     }

@@ -290,6 +290,32 @@ __device__ __forceinline__ void exp_neg_block(const float (&x)[kU], float (&out)
 }
 __device__ __forceinline__ float exp_neg(float x) { return __expf(-x); }
 
+// pi B(nu, T) for the column prologue, which evaluates it ~4000 times per column (every long-wave band at every
+// interface and cell centre): K = h f / k_B and N = pi 100 c 2 h f^3 / c^2 come per band (f = 100 c nu), rT = 1 / T per
+// level, so what is left is exp(K rT) with the kernel's own polynomial, a reciprocal by two Newton steps on
+// rcp.approx and two multiplies -- ~30 instructions where B_wavenumber's expression with libdevice exp and two IEEE
+// divisions takes ~120 (real_gas.py:14-42; agreement ~1e-15, the stand-alone Planck entry points keep that expression).
+__device__ __forceinline__ double rcp_fast(double d) {          // d normal and positive
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
+    r = fma(r, fma(-d, r, 1.0), r);
+    return fma(r, fma(-d, r, 1.0), r);
+}
+__device__ __forceinline__ double planck_fast(double K, double N, double rT) {
+    const double u = fmin(K * rT, 708.0);                       // beyond: B < 1e-290, nothing at any tolerance here
+    return N * rcp_fast(exp_neg(-u) - 1.0);
+}
+__device__ __forceinline__ void planck_band_constants(const PlanckConst &pc, double nu, double &K, double &N) {
+    const double f = 100.0 * nu * pc.c;
+    K = pc.h * f / pc.kB;
+    N = M_PI * (100.0 * pc.c) * (2.0 * pc.h * (f * f * f) / (pc.c * pc.c));
+}
+
+__device__ __forceinline__ double shfl_f64(double v, int src) {
+    const int lo = __shfl_sync(0xffffffffu, __double2loint(v), src), hi = __shfl_sync(0xffffffffu, __double2hiint(v), src);
+    return __hiloint2double(hi, lo);
+}
+
 // Sum eight per-lane values over the warp at once: three exchange steps that halve the number
 // of values a lane carries while doubling the lanes each partial sum covers, then two plain
 // butterfly steps -- 9 additions and 9 shuffles for 8 sums instead of 40 + 40.  Afterwards
@@ -1317,6 +1343,28 @@ __global__ void __launch_bounds__(variant_threads<Real>(V), 1) flux_kernel(const
         for (int i = lane; i < Lp * 32; i += 32) ts[i] = Real(0);
     }
 
+    // Static band data the column prologue walks, in registers for up to 64 bands: which bands are long-wave (a bit
+    // mask) and the band centres (lane l holds bands l and l + 32, broadcast with shuffles).  Read through global
+    // memory they cost an L2 round trip each and one after the other -- the CTA's shared memory leaves almost no L1.
+    const bool meta_regs = a.B <= 64;
+    unsigned long long lwmask = 0ULL;
+    double bK0 = 1.0, bK1 = 1.0, bN0 = 0.0, bN1 = 0.0;          // Planck constants of bands lane, lane + 32
+    if (meta_regs) {
+        const bool l0 = lane < a.B && !a.band_sw[lane < a.B ? lane : 0], l1 = lane + 32 < a.B && !a.band_sw[lane + 32 < a.B ? lane + 32 : 0];
+        lwmask = (unsigned long long)__ballot_sync(0xffffffffu, l0) | ((unsigned long long)__ballot_sync(0xffffffffu, l1) << 32);
+        if (lane < a.B) planck_band_constants(a.pc, a.band_centre[lane], bK0, bN0);
+        if (lane + 32 < a.B) planck_band_constants(a.pc, a.band_centre[lane + 32], bK1, bN1);
+    }
+    auto band_is_sw = [&](int j) { return meta_regs ? !((lwmask >> j) & 1ULL) : (bool)__ldg(a.band_sw + j); };
+    auto band_KN = [&](int j, double &K, double &N) {             // whole warp, uniform j
+        if (meta_regs) {
+            K = shfl_f64(j < 32 ? bK0 : bK1, j & 31);
+            N = shfl_f64(j < 32 ? bN0 : bN1, j & 31);
+        } else {
+            planck_band_constants(a.pc, __ldg(a.band_centre + j), K, N);
+        }
+    };
+
     // Tasks are handed out through a global counter: SMs differ a little in speed (L2 distance,
     // table rows hit), and a static split would leave the fast ones idle at the end.
     __shared__ unsigned long long s_task;
@@ -1370,6 +1418,7 @@ __global__ void __launch_bounds__(variant_threads<Real>(V), 1) flux_kernel(const
             }
         }
 
+        const long long t_lev = a.dbg ? clock64() : 0;
         // ---- emission coefficients of the long-wave bands this CTA touches (real_gas.py:634-638) -----
         const int sA = a.part_seg0[cpart * W], sB = a.part_seg0[(cpart + 1) * W];
         const double Tg = a.T_g[col];
@@ -1378,9 +1427,14 @@ __global__ void __launch_bounds__(variant_threads<Real>(V), 1) flux_kernel(const
         double *bsrc = (double *)(smem_raw + lay.off_bsrc);       // kVarRedTmem: boundary sources of every band, once per column
         if constexpr (RT)
             for (int j = tid; j < a.B; j += nthr) {
-                const double c = __ldg(a.band_centre + j);
-                bsrc[j] = M_PI * planck_wavenumber(a.pc, c, Tg);                          // :638
-                bsrc[a.B + j] = M_PI * planck_wavenumber(a.pc, c, a.T_star) * solar;      // :640-642
+                double K, N;
+                if (meta_regs) {                                  // j = tid here: this lane's band
+                    K = j < 32 ? bK0 : bK1, N = j < 32 ? bN0 : bN1;
+                } else {
+                    planck_band_constants(a.pc, __ldg(a.band_centre + j), K, N);
+                }
+                bsrc[j] = planck_fast(K, N, 1.0 / Tg);                                    // :638
+                bsrc[a.B + j] = planck_fast(K, N, 1.0 / a.T_star) * solar;                // :640-642
             }
         if (sA < sB) {
             // Lane = one layer of a 31-layer chunk (lane 31 only supplies B at the next interface); the
@@ -1393,6 +1447,7 @@ __global__ void __launch_bounds__(variant_threads<Real>(V), 1) flux_kernel(const
                 const int k = ch * 31 + lane;
                 const double Ti = k < L ? (k == L - 1 ? Tg : a.Tint[col * L + k]) : 1.0;      // :636
                 const double Tc = k < nl ? a.T[col * nl + k] : 1.0;
+                const double rTi = rcp_fast(Ti), rTc = rcp_fast(Tc);
                 const bool writer = lane < 31 && k < nl;
                 double gw[10];
 #pragma unroll
@@ -1409,24 +1464,28 @@ __global__ void __launch_bounds__(variant_threads<Real>(V), 1) flux_kernel(const
                 };
                 int pend = -1;                                      // a long-wave band waiting for a partner
                 for (int j = jA + grp; j <= jB; j += groups) {
-                    if (__ldg(a.band_sw + j)) continue;
+                    if (band_is_sw(j)) continue;
                     if (pend < 0) {
                         pend = j;
                         continue;
                     }
-                    const double c0 = __ldg(a.band_centre + pend), c1 = __ldg(a.band_centre + j);
-                    const double bi0 = M_PI * planck_wavenumber(a.pc, c0, Ti), bi1 = M_PI * planck_wavenumber(a.pc, c1, Ti);
-                    const double bc0 = M_PI * planck_wavenumber(a.pc, c0, Tc), bc1 = M_PI * planck_wavenumber(a.pc, c1, Tc);
+                    double K0, N0, K1, N1;
+                    band_KN(pend, K0, N0);
+                    band_KN(j, K1, N1);
+                    const double bi0 = planck_fast(K0, N0, rTi), bi1 = planck_fast(K1, N1, rTi);
+                    const double bc0 = planck_fast(K0, N0, rTc), bc1 = planck_fast(K1, N1, rTc);
                     one_band(pend, bi0, bc0);
                     one_band(j, bi1, bc1);
                     pend = -1;
                 }
                 if (pend >= 0) {
-                    const double c0 = __ldg(a.band_centre + pend);
-                    one_band(pend, M_PI * planck_wavenumber(a.pc, c0, Ti), M_PI * planck_wavenumber(a.pc, c0, Tc));
+                    double K0, N0;
+                    band_KN(pend, K0, N0);
+                    one_band(pend, planck_fast(K0, N0, rTi), planck_fast(K0, N0, rTc));
                 }
             }
         }
+        const long long t_coef = a.dbg ? clock64() : 0;
         __syncthreads();
 
         // ---- this warp's run of segments -------------------------------------------------------------
@@ -1544,6 +1603,7 @@ __global__ void __launch_bounds__(variant_threads<Real>(V), 1) flux_kernel(const
         if (dbg_here) {
             a.dbg[warp] = clock64() - t_sweep0;
             a.dbg[32 + warp] = t_sweep0 - t_task0;
+            if (warp < 4) a.dbg[60 + warp] = warp == 0 ? t_lev - t_task0 : warp == 1 ? t_coef - t_lev : warp == 2 ? t_coef - t_task0 : t_lev - t_task0;
         }
         if (C != 1) continue;      // several CTAs per column: flux_band_sums_kernel + flux_net_kernel finish
 
