@@ -1514,11 +1514,26 @@ __global__ void __launch_bounds__(variant_threads<Real>(V), 1) flux_kernel(const
             seg_params(s, wN, srcN);
             prefetch_pass<Real, MM>(up, Lp, srcN, lv, fd);
         }
+        // Parameters of a (warp, band) run -- band, first chain, band length, sum of the nu-weights -- come from global
+        // memory through two dependent loads; those of the NEXT run are requested when a run starts and arrive
+        // behind its passes.
+        int rj = 0, rc0 = 0, rlen = 0;
+        double rsumw = 0.0;
+        auto load_run = [&](int sidx, int &j_, int &c0_, int &len_, double &sumw_) {
+            j_ = __ldg(a.seg_band + sidx);
+            c0_ = __ldg(a.seg_c0 + sidx);
+            len_ = __ldg(a.band_len + j_);
+            sumw_ = __ldg(a.band_sumw + j_);
+        };
+        if (s < s1) load_run(s, rj, rc0, rlen, rsumw);
         while (s < s1) {
-            const int j = a.seg_band[s];
+            const int j = rj;
             // the run ends with the band (its remaining chains, 32 per segment) or with this warp's share
-            const int e = min(s1, s + ((__ldg(a.band_len + j) - __ldg(a.seg_c0 + s) + 31) >> 5));
-            const bool lw = !__ldg(a.band_sw + j);
+            const int e = min(s1, s + ((rlen - rc0 + 31) >> 5));
+            const bool first_chain = rc0 == 0;
+            const double sumw = rsumw;
+            if (e < s1) load_run(e, rj, rc0, rlen, rsumw);
+            const bool lw = !band_is_sw(j);
             Real bg, bs;
             if constexpr (RT) {
                 bg = (Real)bsrc[j];
@@ -1537,9 +1552,8 @@ __global__ void __launch_bounds__(variant_threads<Real>(V), 1) flux_kernel(const
                 coef = cw;
             }
             // boundary terms: Trans(i,i) = sum of the nu-weights
-            const bool first_chain = __ldg(a.seg_c0 + s) == 0;
-            const double bnd_up = first_chain ? (double)bg * a.band_sumw[j] : 0.0;
-            const double bnd_dn = first_chain ? (double)bs * a.band_sumw[j] : 0.0;
+            const double bnd_up = first_chain ? (double)bg * sumw : 0.0;
+            const double bnd_dn = first_chain ? (double)bs * sumw : 0.0;
             if (first_chain && lane == 0) {
                 bacc_up[L - 1] += bnd_up;
                 bacc_dn[0] += bnd_dn;
