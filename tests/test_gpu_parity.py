@@ -400,13 +400,18 @@ def test_errors():
 
 
 # ---- shapes at the edges of the kernel's decomposition -------------------------------------------------
+@pytest.mark.parametrize('precision', ['f64', 'f32'])
 @pytest.mark.parametrize('L,M,N,B', [(5, 1, 70, 3), (9, 2, 333, 7), (10, 3, 97, 2), (17, 4, 500, 11),
                                       (150, 2, 640, 9), (230, 1, 200, 5)])
-def test_shapes_against_oracle(L, M, N, B):
+def test_shapes_against_oracle(L, M, N, B, precision):
     """Level counts below / at / off the 8-layer block size and beyond what 8 warps' t-stores fit
     (fewer warps per CTA), 1-4 molecules, ragged bands (1-bin bands, bands that are not a
     multiple of 32 bins, a long-wave band spanning several segments), few and many columns, both
-    optical-depth sources: against the oracle's evaluation of the reference algorithm."""
+    optical-depth sources: against the oracle's evaluation of the reference algorithm.  In FP32 mode the
+    same shapes exercise the 12-warp direct passes (three warps per lane quarter of tensor memory) and their
+    fall-backs when the t-stores of 12 warps do not fit (L = 150, 230)."""
+    tol = TOL64 if precision == 'f64' else TOL32
+    eps = np.finfo(float).eps if precision == 'f64' else np.finfo(np.float32).eps
     rng = np.random.default_rng(100 * L + M)
     P = np.sort(np.logspace(np.log10(101320.), np.log10(30.), L))
     nu = 10.0 + np.arange(N) * 7.0
@@ -421,7 +426,7 @@ def test_shapes_against_oracle(L, M, N, B):
     tabs = [{'p': np.logspace(5.1, 1, 12 + m), 'T': np.linspace(180., 320., 3 + m), 'nu': nu,
              'absorption_coef': 10 ** rng.uniform(-7, 1, (12 + m, 3 + m, N))} for m in range(M)]
     from climatemodel_b200.plan import FluxPlan
-    plan = FluxPlan(P, nu, bands, tables=tabs)
+    plan = FluxPlan(P, nu, bands, tables=tabs, precision=precision)
     c = {'P': P, 'nu': nu, 'tables': tabs, 'bands': bands, 'T_star': 5778., 'R_star': 6.96340e8,
          'dist': 1.495978707e11, 'band_delta': bands['delta']}
     for n_col in (1, 3, 400):
@@ -433,12 +438,12 @@ def test_shapes_against_oracle(L, M, N, B):
         out = plan.flux(T, T_g, T_tau=T_tau, q=q, albedo=albedo)
         for i in sorted({0, n_col // 2, n_col - 1}):
             up, dn, net, heat = oracle_column(c, T[i], T_g[i], T_tau[i], albedo[i], q[:, i])
-            assert relmax(out['up'][i], up) < TOL64
-            assert relmax(out['down'][i], dn) < TOL64
-            assert relmax(out['net'][i], net) < TOL64
-            assert heating_ok(out['heating'][i], heat, up, dn, c['band_delta'], c['P'], TOL64)
+            assert relmax(out['up'][i], up) < tol
+            assert relmax(out['down'][i], dn) < tol
+            assert relmax(out['net'][i], net) < tol
+            assert heating_ok(out['heating'][i], heat, up, dn, c['band_delta'], c['P'], tol, eps=eps)
         # the resident-tau source with the tau of column 0 for every column
         tau0 = orc.optical_depth(P, T_tau[0], nu, tabs, list(q[:, 0]))
         res = plan.flux(T, T_g, tau=tau0, albedo=albedo, outputs=('net',))['net']
         up, dn = orc.get_flux(P, T[-1], T_g[-1], tau0, nu, bands, albedo=albedo[-1])
-        assert relmax(res[-1], orc.net_flux(up, dn, bands['delta'])) < TOL64
+        assert relmax(res[-1], orc.net_flux(up, dn, bands['delta'])) < tol
