@@ -1630,18 +1630,20 @@ __global__ void __launch_bounds__(variant_threads<Real>(V), 1) flux_kernel(const
             double acc = 0.0;
             if (!out) {     // only net / heating wanted: independent loads, slot by slot
                 const double *v = sc + half * (int64_t)L + i;
-                int q = 0;
-                for (; q + 8 <= a.n_slots; q += 8) {
-                    double x[8], d[8];
+                // sixteen slots in flight at a time (the scratch is L2 resident: a batch costs one L2 round trip);
+                // the sum itself stays in slot order
+                for (int q = 0; q < a.n_slots; q += 16) {
+                    double x[16], d[16];
 #pragma unroll
-                    for (int r = 0; r < 8; ++r) {
-                        x[r] = v[(q + r) * 2 * (int64_t)L];
-                        d[r] = __ldg(a.slot_delta + q + r);
+                    for (int r = 0; r < 16; ++r) {
+                        const int qq = min(q + r, a.n_slots - 1);
+                        x[r] = v[qq * 2 * (int64_t)L];
+                        d[r] = __ldg(a.slot_delta + qq);
                     }
 #pragma unroll
-                    for (int r = 0; r < 8; ++r) acc = fma(x[r], d[r], acc);
+                    for (int r = 0; r < 16; ++r)
+                        if (q + r < a.n_slots) acc = fma(x[r], d[r], acc);
                 }
-                for (; q < a.n_slots; ++q) acc = fma(v[q * 2 * (int64_t)L], __ldg(a.slot_delta + q), acc);
             } else
             for (int j = a.band_lo; j < a.band_hi; ++j) {
                 double sum = 0.0;
