@@ -44,12 +44,13 @@ static double cost_knob(const char *name, double dflt) {
 // Pass costs in units of one short-wave fresh pass, fitted to per-warp cycle counts (CMB200_DEBUG_TIMING) of the
 // kernel family: a long-wave fresh pass, and what a (part, band) run adds at its end (replay-only pass, write-out
 // of the partial sums) for short- and long-wave bands.  Model 1 = direct short-wave passes with the tensor-memory
-// lane sum (their short-wave pass is cheaper, so everything else weighs more), model 0 = the other kernels.
+// lane sum (their short-wave pass is cheaper, so everything else weighs more) in FP64, model 2 = the same in FP32
+// (a long-wave pass, still the round-1 form, weighs two short-wave ones), model 0 = the other kernels.
 struct PassCosts {
     double lw, run_sw, run_lw;
 };
 static PassCosts pass_costs(int model) {
-    PassCosts c = model == 1 ? PassCosts{1.7, 0.65, 0.7} : PassCosts{1.5, 0.4, 0.6};
+    PassCosts c = model == 1 ? PassCosts{1.7, 0.65, 0.7} : model == 2 ? PassCosts{2.0, 0.65, 0.65} : PassCosts{1.5, 0.4, 0.6};
     c.lw = cost_knob("CMB200_COST_LW", c.lw);
     c.run_sw = cost_knob("CMB200_COST_RUN_SW", c.run_sw);
     c.run_lw = cost_knob("CMB200_COST_RUN_LW", c.run_lw);
@@ -247,7 +248,7 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     int ctas_per_sm = 1;
     CMB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, flux_kernel<Real, MM, V>, W * 32, smem));
     const int resident = sm_count(p->device) * std::max(1, ctas_per_sm);
-    int rc = ensure_partition(p, io->n_col, W, resident, (V & kVarRedTmem) ? 1 : 0);
+    int rc = ensure_partition(p, io->n_col, W, resident, (V & kVarRedTmem) ? (std::is_same<Real, double>::value ? 1 : 2) : 0);
     if (rc) return rc;
     const Partition &pt = p->partition;
     if (pt.n_slots == 0) {     // no segment in this plan's band / segment range: every sum is empty
