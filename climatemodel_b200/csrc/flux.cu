@@ -45,12 +45,17 @@ static double cost_knob(const char *name, double dflt) {
 // kernel family: a long-wave fresh pass, and what a (part, band) run adds at its end (replay-only pass, write-out
 // of the partial sums) for short- and long-wave bands.  Model 1 = direct short-wave passes with the tensor-memory
 // lane sum (their short-wave pass is cheaper, so everything else weighs more) in FP64, model 2 = the same in FP32
-// (a long-wave pass, still the round-1 form, weighs two short-wave ones), model 0 = the other kernels.
+// (a long-wave pass, still the round-1 form, weighs two short-wave ones), model 3 = FP32 with two segments per
+// short-wave pass (the unit is then half a pair pass; part boundaries inside a short-wave band are moved so that a
+// part's share of the band is a whole number of pairs), model 0 = the other kernels.
 struct PassCosts {
     double lw, run_sw, run_lw;
 };
 static PassCosts pass_costs(int model) {
-    PassCosts c = model == 1 ? PassCosts{1.7, 0.65, 0.7} : model == 2 ? PassCosts{2.0, 0.65, 0.65} : PassCosts{1.5, 0.4, 0.6};
+    PassCosts c = model == 1   ? PassCosts{1.7, 0.65, 0.7}
+                  : model == 2 ? PassCosts{2.0, 0.65, 0.65}
+                  : model == 3 ? PassCosts{1.7, 1.0, 1.8}
+                               : PassCosts{1.5, 0.4, 0.6};
     c.lw = cost_knob("CMB200_COST_LW", c.lw);
     c.run_sw = cost_knob("CMB200_COST_RUN_SW", c.run_sw);
     c.run_lw = cost_knob("CMB200_COST_RUN_LW", c.run_lw);
@@ -79,10 +84,14 @@ static int ensure_partition(cmb200_plan *p, int64_t n_col, int W, int resident_c
     const int parts = C * W, n_seg = p->n_seg;
     const PassCosts pc = pass_costs(cost_model);
     std::vector<double> prefix(n_seg + 1, 0.0);
+    int band_first = 0;
     for (int s = 0; s < n_seg; ++s) {
         const int j = p->hseg_band[s];
+        const bool band_start = s == 0 || p->hseg_band[s - 1] != j;
+        if (band_start) band_first = s;
         double c = p->hsw[j] ? 1.0 : pc.lw;
-        if (s == 0 || p->hseg_band[s - 1] != j) c += p->hsw[j] ? pc.run_sw : pc.run_lw;
+        if (cost_model == 3 && p->hsw[j]) c = ((s - band_first) & 1) ? 0.0 : 2.0;     // a pair pass starts at even offsets
+        if (band_start) c += p->hsw[j] ? pc.run_sw : pc.run_lw;
         prefix[s + 1] = prefix[s] + c;
     }
     std::vector<int32_t> seg0(parts + 1), slot0(parts), bslot(p->B + 1, 0);
@@ -94,6 +103,16 @@ static int ensure_partition(cmb200_plan *p, int64_t n_col, int W, int resident_c
     }
     seg0[0] = 0;
     seg0[parts] = n_seg;
+    if (cost_model == 3)
+        for (int i = 1; i < parts; ++i) {
+            const int b = seg0[i];
+            if (b <= seg0[i - 1] || b >= n_seg) continue;
+            const int j = p->hseg_band[b];
+            if (!p->hsw[j] || p->hseg_band[b - 1] != j) continue;        // not inside a short-wave band
+            int first = b;                                              // start of the previous part's share of band j
+            while (first > seg0[i - 1] && p->hseg_band[first - 1] == j) --first;
+            if ((b - first) & 1) seg0[i] = std::min(b + 1, seg0[i + 1]);
+        }
     std::vector<int32_t> slot_band;
     for (int i = 0; i < parts; ++i) {
         slot0[i] = (int32_t)slot_band.size();
@@ -127,7 +146,7 @@ static int ensure_partition(cmb200_plan *p, int64_t n_col, int W, int resident_c
 // by the warps w, w + 4, ...  0 = the variant cannot run this L.
 template <typename Real, int MM, int V>
 static int variant_warps(int L, int max_smem, int *tmem_cpw, int *tmem_cols) {
-    const int Lp = padded_layers(L), wpr = (int)(sizeof(Real) / 4);
+    const int Lp = padded_layers(L), wpr = variant_tstore_words<Real>(V);
     *tmem_cpw = *tmem_cols = 0;
     int most = 8;
     if (V & kVarTmem) {
@@ -159,7 +178,7 @@ constexpr int kReferenceVariant = kVarTmem | kVarCoefSmem;
 template <typename Real, int MM>
 constexpr int default_variant() {
     constexpr int direct = kVarSwDirect | kVarRedTmem | kVarSmallSt;      // table-fused path: direct short-wave passes
-    if (!std::is_same<Real, double>::value) return MM > 0 ? (kReferenceVariant | direct) : kReferenceVariant;
+    if (!std::is_same<Real, double>::value) return MM > 0 ? (kReferenceVariant | direct | kVarPair) : kReferenceVariant;
     return MM > 0 ? (kReferenceVariant | kVarExpLds | direct) : (kReferenceVariant | kVarExpLds);
 }
 #ifndef CMB_FLUX_EXPERIMENTS
@@ -181,18 +200,21 @@ static bool ensure_segment_table(cmb200_plan *p, cudaStream_t s) {
     const char *e = getenv("CMB200_SEGMENT_TABLE");
     if ((e && *e == '0') || p->n_seg == 0) return false;
     if (p->ks_valid) return true;
-    const int64_t spitch = (int64_t)p->n_seg * 32, rows = (int64_t)p->M * p->L * p->nT_pad;
+    // one segment of zero padding per row: a pair pass (kVarPair) reads the segment after its last one, with weight 0
+    const int64_t spitch = ((int64_t)p->n_seg + 1) * 32, rows = (int64_t)p->M * p->L * p->nT_pad;
     const Real *KL;
     Real *KS;
     if constexpr (std::is_same<Real, double>::value) {
         if (p->KS64.alloc((size_t)rows * spitch) != cudaSuccess) return cudaGetLastError(), false;
         KL = p->KL64.p, KS = p->KS64.p;
+        if (cudaMemsetAsync(KS, 0, (size_t)rows * spitch * sizeof(Real), s) != cudaSuccess) return false;
     } else {
         if (p->KS32.alloc((size_t)rows * spitch) != cudaSuccess) return cudaGetLastError(), false;
         KL = p->KL32.p, KS = p->KS32.p;
+        if (cudaMemsetAsync(KS, 0, (size_t)rows * spitch * sizeof(Real), s) != cudaSuccess) return false;
     }
     dim3 grid((unsigned)((spitch + 255) / 256), (unsigned)std::min<int64_t>(rows, 65535));
-    segment_table_kernel<Real><<<grid, 256, 0, s>>>(KL, rows, p->pitch, p->seg_bin.p, spitch, KS);
+    segment_table_kernel<Real><<<grid, 256, 0, s>>>(KL, rows, p->pitch, p->seg_bin.p, (int64_t)p->n_seg * 32, spitch, KS);
     if (cudaGetLastError() != cudaSuccess) return false;
     g_launches.fetch_add(1);
     p->spitch = spitch;
@@ -214,6 +236,9 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     CMB_CUDA(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, p->device));
     int tmem_cpw = 0, tmem_cols = 0;
     const int W = variant_warps<Real, MM, V>(L, max_smem, &tmem_cpw, &tmem_cols);
+    if constexpr ((V & kVarPair) != 0) {      // pair passes: segment-space table and two warps per lane quarter, else one segment per pass
+        if (!seg_space || W < 8 || (W / 4) * (tmem_cpw + 2 * kU) > tmem_cols) return launch_flux<Real, MM, V & ~kVarPair>(p, io, Tint, s);
+    }
     if constexpr (V != 0) {      // the variant has to offer at least the warps of the plain kernel, else that one runs
         int c0, c1;
         if (W < variant_warps<Real, MM, 0>(L, max_smem, &c0, &c1)) return launch_flux<Real, MM, 0>(p, io, Tint, s);
@@ -229,13 +254,13 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     if constexpr ((V & kVarRedTmem) != 0 && !std::is_same<Real, double>::value) {
         // FP32: no exp table, everything contiguous; the exchange columns follow the t-stores in tensor memory
         if (lay.total(W) + 1024 > (size_t)max_smem || (W / 4) * (tmem_cpw + 2 * kU) > tmem_cols)
-            return launch_flux<Real, MM, V & ~(kVarSwDirect | kVarRedTmem | kVarSmallSt)>(p, io, Tint, s);
+            return launch_flux<Real, MM, V & ~(kVarSwDirect | kVarRedTmem | kVarSmallSt | kVarPair)>(p, io, Tint, s);
     } else if constexpr ((V & kVarSwDirect) != 0 && std::is_same<Real, double>::value) {
         // the exp table occupies shared-window addresses [xl_window, xl_window + 64 kB): the level tables and the
         // warps' regions have to end below it (the window starts at a small driver-reserved offset)
         constexpr unsigned win = xl_window(V);
         if (lay.total(W) + 2048 > win || (size_t)max_smem < (size_t)win + kXlBytes)
-            return launch_flux<Real, MM, V & ~(kVarSwDirect | kVarRedTmem | kVarSmallSt)>(p, io, Tint, s);
+            return launch_flux<Real, MM, V & ~(kVarSwDirect | kVarRedTmem | kVarSmallSt | kVarPair)>(p, io, Tint, s);
         smem = (size_t)win + kXlBytes;
         if constexpr ((V & kVarRedTmem) != 0) {
             // the warps' coefficient rows sit above the table; the exchange columns follow the t-stores in tensor memory
@@ -248,7 +273,8 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     int ctas_per_sm = 1;
     CMB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, flux_kernel<Real, MM, V>, W * 32, smem));
     const int resident = sm_count(p->device) * std::max(1, ctas_per_sm);
-    int rc = ensure_partition(p, io->n_col, W, resident, (V & kVarRedTmem) ? (std::is_same<Real, double>::value ? 1 : 2) : 0);
+    int rc = ensure_partition(p, io->n_col, W, resident,
+                              (V & kVarPair) ? 3 : (V & kVarRedTmem) ? (std::is_same<Real, double>::value ? 1 : 2) : 0);
     if (rc) return rc;
     const Partition &pt = p->partition;
     if (pt.n_slots == 0) {     // no segment in this plan's band / segment range: every sum is empty
@@ -429,6 +455,9 @@ static int launch_flux_variant(int variant, cmb200_plan *plan, const cmb200_flux
     if constexpr ((default_variant<Real, MM>() & kVarRedTmem) != 0 && std::is_same<Real, double>::value)
         if (variant == (default_variant<Real, MM>() & ~(kVarRedTmem | kVarSmallSt)))
             return launch_flux<Real, MM, default_variant<Real, MM>() & ~(kVarRedTmem | kVarSmallSt)>(plan, io, Tint, s);
+    if constexpr ((default_variant<Real, MM>() & kVarPair) != 0)         // FP32: one segment per pass on 12 warps (A/B)
+        if (variant == (default_variant<Real, MM>() & ~kVarPair))
+            return launch_flux<Real, MM, default_variant<Real, MM>() & ~kVarPair>(plan, io, Tint, s);
     return launch_flux<Real, MM, default_variant<Real, MM>()>(plan, io, Tint, s);
 }
 

@@ -91,7 +91,9 @@ constexpr int kVarTmem = 1, kVarCoefSmem = 2;
 //                 (warp, band) run is written out.  Short-wave replay-only passes take the same route (sw_replay_pass).
 //   kVarSmallSt   (with kVarSwDirect) the direct short-wave passes store their blocks to tensor memory with eight
 //                 STTM.x2 (the register pair of each value) instead of one STTM.x16.
-constexpr int kVarExpLds = 1024, kVarSwDirect = 4096, kVarRedTmem = 8192, kVarSmallSt = 16384;
+//   kVarPair      (FP32, with kVarRedTmem) a short-wave pass carries TWO consecutive segments per lane in packed FP32
+//                 arithmetic (FFMA2 / FMUL2 / FADD2), see sw_fresh_pair_pass; 8 warps per SM.
+constexpr int kVarExpLds = 1024, kVarSwDirect = 4096, kVarRedTmem = 8192, kVarSmallSt = 16384, kVarPair = 32768;
 // Class accumulators of kVarRedTmem: [2 directions][Lp / kU blocks][32 lanes] double2 (x: layer u, y: layer u + 4 of the
 // block, u = lane & 3; class c = lane >> 2): every thread owns slot `lane` of every block, so a warp's LDS.128 /
 // STS.128 covers 512 contiguous bytes in lane order (no bank conflicts).
@@ -111,11 +113,16 @@ struct ExpAux {
     const double *lds;
     unsigned saddr;       // kVarSwDirect: xl_window(V) | (lane & 15) * 8
 };
-// Threads per CTA the kernel is compiled for: 8 warps, or 12 (168 registers) for the FP32 direct passes, whose
-// t-stores are half as wide (three warps per lane quarter of tensor memory instead of two).
+// Threads per CTA the kernel is compiled for: 8 warps, or 12 (168 registers) for the FP32 direct passes with one
+// segment per pass, whose t-stores are half as wide (three warps per lane quarter of tensor memory instead of two).
 template <typename Real>
 constexpr int variant_threads(int V) {
-    return (sizeof(Real) == 4 && (V & 8192)) ? 384 : 256;
+    return (sizeof(Real) == 4 && (V & 8192) && !(V & 32768)) ? 384 : 256;
+}
+// Tensor-memory words per layer and lane of the t-store.
+template <typename Real>
+constexpr int variant_tstore_words(int V) {
+    return (sizeof(Real) == 4 && (V & 32768)) ? 2 : (int)(sizeof(Real) / 4);
 }
 
 constexpr int kU = 8;          // layers per block of a pass (instruction-level parallelism)
@@ -1236,6 +1243,204 @@ __device__ __forceinline__ void sw_fresh_pass(const int lane, const int nl, cons
     }
 }
 
+// ---- FP32, two segments per pass (kVarPair) -------------------------------------------------------------
+// The FP32 passes are bound by instruction issue, not by any pipe.  Blackwell's packed FP32 instructions (FFMA2 /
+// FMUL2 / FADD2: two FP32 operations on a register pair, a 32-bit operand is broadcast for free) halve the issue
+// slots of the arithmetic, so a lane carries the same chain of TWO consecutive segments of a band (.x = segment s,
+// .y = segment s + 1: in segment space its table values sit 128 bytes apart, one address for both loads).  Per
+// layer and lane everything is then two words wide -- the t-store, the parked values, the transposing loads are
+// those of the FP64 kernel -- and a warp needs FP64's share of tensor memory: 8 warps per SM instead of 12.
+using f2 = float2;
+__device__ __forceinline__ f2 f2_set(float a) { return make_float2(a, a); }
+__device__ __forceinline__ f2 f2_mul(f2 a, f2 b) { return __fmul2_rn(a, b); }
+__device__ __forceinline__ f2 f2_add(f2 a, f2 b) { return __fadd2_rn(a, b); }
+__device__ __forceinline__ f2 f2_fma(f2 a, f2 b, f2 c) { return __ffma2_rn(a, b, c); }
+__device__ __forceinline__ f2 f2_ld(const char *p) {      // segments s and s + 1, this lane
+    return make_float2(*(const float *)p, *(const float *)(p + 128));
+}
+template <int MM>
+struct PairFeed {
+    f2 raw[kU][MM > 0 ? MM : 1];
+    f2 icraw[MM > 0 ? MM : 1];
+};
+template <int MM>
+__device__ __forceinline__ void prefetch_pair_pass(const bool up, const int Lp, const void *src_lane,
+                                                   const LevelView<float> &lv, PairFeed<MM> &fd) {
+    const char *src_bytes = (const char *)src_lane;
+    const unsigned *offs = up ? lv.off_up : lv.off_dn;
+    const int k0 = up ? Lp - kU : 0, kc = (up ? Lp : 0) + kLevShift;
+#pragma unroll
+    for (int m = 0; m < MM; ++m) {
+        unsigned off[kU];
+        lds_block(offs + m * lv.stride + k0 + 4, off);
+#pragma unroll
+        for (int u = 0; u < kU; ++u) fd.raw[u][m] = f2_ld(src_bytes + (size_t)off[u] * 16u);
+        fd.icraw[m] = f2_ld(src_bytes + (size_t)lv.off_dn[m * lv.stride + kc] * 16u);
+    }
+}
+template <bool SMALL>
+__device__ __forceinline__ void tm_store_block(uint32_t addr, const f2 (&v)[kU]) {
+    if constexpr (SMALL) {
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+            uint32_t q[2] = {__float_as_uint(v[u].x), __float_as_uint(v[u].y)};
+            tmem::st_small<2>(addr + (uint32_t)(2 * u), q);
+        }
+    } else {
+        uint32_t w[2 * kU];
+#pragma unroll
+        for (int u = 0; u < kU; ++u) w[2 * u] = __float_as_uint(v[u].x), w[2 * u + 1] = __float_as_uint(v[u].y);
+        tmem::st<2 * kU>(addr, w);
+    }
+}
+__device__ __forceinline__ void unpack_pairs(const uint32_t (&w)[2 * kU], f2 (&v)[kU]) {
+#pragma unroll
+    for (int u = 0; u < kU; ++u) v[u] = make_float2(__uint_as_float(w[2 * u]), __uint_as_float(w[2 * u + 1]));
+}
+// The transposed words are those of an FP64 block (RedQ<double>): value u / u + 4 of lanes c, c + 8 | c + 16, c + 24,
+// each value the pair of the lane's two segments.  Four lanes and both segments in FP32, FP64 from there on.
+__device__ __forceinline__ void red_accumulate_pairs(const RedQ<double> &r, double2 acc, unsigned slot) {
+    auto f = [](const uint32_t(&q)[8], int i) { return make_float2(__uint_as_float(q[2 * i]), __uint_as_float(q[2 * i + 1])); };
+    const f2 lo = f2_add(f2_add(f(r.q0, 0), f(r.q0, 1)), f2_add(f(r.q1, 0), f(r.q1, 1)));
+    const f2 hi = f2_add(f2_add(f(r.q0, 2), f(r.q0, 3)), f2_add(f(r.q1, 2), f(r.q1, 3)));
+    acc.x += (double)(lo.x + lo.y);
+    acc.y += (double)(hi.x + hi.y);
+    red_slot_store(slot, acc);
+}
+
+// sw_fresh_pass for a segment pair (always with the tensor-memory lane sum).
+template <int MM, bool UP, int V>
+__device__ __forceinline__ void sw_fresh_pair_pass(const int Lp, const f2 wF, const f2 wR, const float b0,
+                                                   const void *src_lane, const void *next_src, PairFeed<MM> &fd,
+                                                   const LevelView<float> lv, const uint32_t taddr, const RedAux ra) {
+    static_assert(MM > 0, "table-fused path");
+    constexpr bool SMALL = (V & kVarSmallSt) != 0;
+    constexpr int NW = 2 * kU;
+    const int kfirst = UP ? Lp - kU : 0, kstep = UP ? -kU : kU, nb = Lp / kU;
+    const char *src_bytes = (const char *)src_lane;
+    const unsigned s0 = (unsigned)__cvta_generic_to_shared(smem_raw);
+    const unsigned s_offs = (unsigned)__cvta_generic_to_shared(UP ? lv.off_up : lv.off_dn) - s0;
+    const unsigned s_qg = (unsigned)__cvta_generic_to_shared(lv.qg) - s0, s_hdp = (unsigned)__cvta_generic_to_shared(lv.hdp) - s0;
+
+    f2 EF = f2_mul(wF, f2_set(b0)), ER = f2_mul(wR, f2_set(b0));
+    f2 Ic = f2_set(0.f);
+#pragma unroll
+    for (int m = 0; m < MM; ++m) Ic = f2_fma(f2_set(lv.qg[m * lv.stride + (UP ? Lp : 0) + kLevShift]), fd.icraw[m], Ic);
+
+    f2 v[kU];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) v[u] = f2_set(0.f);
+    const unsigned cbase = UP ? ra.up : ra.dn;
+    unsigned slot = cbase + kfirst * 64;
+    tm_store_block<SMALL>(ra.scratch, v);
+
+    for (int it = 0, k0 = kfirst; it < nb; ++it, k0 += kstep) {
+        auto &raw = fd.raw;
+        uint32_t tRw[NW];
+        tmem::ld<NW>(taddr + (uint32_t)(k0 * 2), tRw);
+        // ---- integrand at the block's loaded interfaces, thickness of its layers --------------------------
+        f2 In[kU], x[kU];
+#pragma unroll
+        for (int m = 0; m < MM; ++m) {
+            float qg[kU];
+            if (UP)
+                lds_real8_m1(s_qg + (unsigned)(m * lv.stride + k0 + kLevShift) * 4u, qg);
+            else
+                lds_real8(s_qg + (unsigned)(m * lv.stride + k0 + 1 + kLevShift) * 4u, qg);
+#pragma unroll
+            for (int u = 0; u < kU; ++u) In[u] = m ? f2_fma(f2_set(qg[u]), raw[u][m], In[u]) : f2_mul(f2_set(qg[u]), raw[u][0]);
+        }
+        {
+            float hd[kU];
+            lds_real8(s_hdp + (unsigned)k0 * 4u, hd);
+#pragma unroll
+            for (int u = 0; u < kU; ++u) {
+                const f2 lo = UP ? In[u] : (u ? In[u - 1] : Ic);
+                const f2 hi = UP ? (u < kU - 1 ? In[u + 1] : Ic) : In[u];
+                x[u] = f2_mul(f2_set(hd[u] * -1.4426950408889634f), f2_add(lo, hi));       // -thickness * log2 e
+            }
+            Ic = UP ? In[0] : In[kU - 1];
+        }
+        // ---- the next block's table values (or the next pass's first block) into the same registers ----------
+        if (it + 1 < nb) {
+#pragma unroll
+            for (int m = 0; m < MM; ++m) {
+                unsigned off[kU];
+                lds_u32x8(s_offs + (unsigned)(m * lv.stride + k0 + kstep + 4) * 4u, off);
+#pragma unroll
+                for (int u = 0; u < kU; ++u) raw[u][m] = f2_ld(src_bytes + (size_t)off[u] * 16u);
+            }
+        } else if (next_src) {
+            prefetch_pair_pass<MM>(!UP, Lp, next_src, lv, fd);
+        }
+        // ---- the previous block's values, transposed, are on their way behind the exp -------------------------
+        RedQ<double> rq;
+        red_fetch(ra.scratch, rq);
+        const double2 cacc = red_slot_load(slot);
+        f2 t[kU];
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+            asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(t[u].x) : "f"(x[u].x));
+            asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(t[u].y) : "f"(x[u].y));
+        }
+        // ---- both recurrences in sweep order; the block's values for the next iteration's lane sum -------------
+        f2 tR[kU];
+        red_wait(tRw, rq);
+        unpack_pairs(tRw, tR);
+        red_accumulate_pairs(rq, cacc, slot);
+#pragma unroll
+        for (int o = 0; o < kU; ++o) {
+            const int u = UP ? kU - 1 - o : o;
+            EF = f2_mul(EF, t[u]);
+            ER = f2_mul(ER, tR[u]);
+            v[u] = f2_add(EF, ER);
+        }
+        tm_store_block<SMALL>(taddr + (uint32_t)(k0 * 2), t);
+        tm_store_block<SMALL>(ra.scratch, v);
+        slot = cbase + k0 * 64;
+    }
+    RedQ<double> rq;
+    red_fetch(ra.scratch, rq);                      // its wait::st also covers the t-store: the next pass reads it back
+    const double2 cacc = red_slot_load(slot);
+    red_wait(rq);
+    red_accumulate_pairs(rq, cacc, slot);
+}
+
+// sw_replay_pass for a segment pair.
+template <bool UP, bool SMALL>
+__device__ __forceinline__ void sw_replay_pair_pass(const int Lp, const f2 wR, const float b0, const uint32_t taddr,
+                                                    const RedAux ra) {
+    constexpr int NW = 2 * kU;
+    const int kfirst = UP ? Lp - kU : 0, kstep = UP ? -kU : kU, nb = Lp / kU;
+    f2 ER = f2_mul(wR, f2_set(b0));
+    uint32_t tw[NW];
+    tmem::ld<NW>(taddr + (uint32_t)(kfirst * 2), tw);
+    for (int it = 0, k0 = kfirst; it < nb; ++it, k0 += kstep) {
+        f2 tR[kU], v[kU];
+        tmem::wait_ld<NW>(tw);
+        unpack_pairs(tw, tR);
+        if (it + 1 < nb) tmem::ld<NW>(taddr + (uint32_t)((k0 + kstep) * 2), tw);
+#pragma unroll
+        for (int o = 0; o < kU; ++o) {
+            const int u = UP ? kU - 1 - o : o;
+            ER = f2_mul(ER, tR[u]);
+            v[u] = ER;
+        }
+        tm_store_block<SMALL>(taddr + (uint32_t)(k0 * 2), v);
+    }
+    tmem::wait_st();
+    const unsigned base = UP ? ra.up : ra.dn;
+    RedQ<double> q;
+    red_fetch_issued(taddr, q);
+    for (int b = 0; b < nb; ++b) {
+        const double2 acc = red_slot_load(base + b * 512);
+        red_wait(q);
+        const RedQ<double> p = q;
+        if (b + 1 < nb) red_fetch_issued(taddr + (uint32_t)((b + 1) * NW), q);
+        red_accumulate_pairs(p, acc, base + b * 512);
+    }
+}
+
 template <typename Real, int MM, bool FRESH, int V>
 __device__ __forceinline__ void dispatch_pass(const bool lw, const bool up, const int lane, const int nl, const int Lp,
                                               const Real wF, const Real wR, const Real bs, const Real bg,
@@ -1277,7 +1482,9 @@ __global__ void __launch_bounds__(variant_threads<Real>(V), 1) flux_kernel(const
     constexpr bool FUSED = MM > 0;
     constexpr int MR = MM > 0 ? MM : 1;
     constexpr bool TM = (V & kVarTmem) != 0, CS = (V & kVarCoefSmem) != 0;
-    constexpr int WPR = sizeof(Real) / 4, NW = kU * WPR;
+    constexpr bool PAIR = sizeof(Real) == 4 && MM > 0 && (V & kVarPair) != 0;
+    static_assert(!(V & kVarPair) || (PAIR && (V & kVarRedTmem) && (V & kVarSwDirect)), "kVarPair: FP32 table-fused direct passes");
+    constexpr int WPR = variant_tstore_words<Real>(V), NW = kU * WPR;
     const int tid = threadIdx.x, nthr = blockDim.x, W = nthr >> 5, warp = tid >> 5, lane = tid & 31;
     const int L = a.L, nl = a.L - 1, Lp = padded_layers(a.L), LS = Lp + kU, C = a.ctas_per_col;
 
@@ -1508,11 +1715,24 @@ __global__ void __launch_bounds__(variant_threads<Real>(V), 1) flux_kernel(const
             }
         };
         PassFeed<Real, MM> fd;
-        Real wN = Real(0);
+        PairFeed<MM> fd2;                   // kVarPair: the feed of a short-wave pair pass
+        Real wN = Real(0), wN1 = Real(0);   // wN1 (kVarPair): weight of the segment after the one wN belongs to
         const void *srcN = nullptr;
+        auto seg_params_pair = [&](int sidx) {
+            seg_params(sidx, wN, srcN);
+            wN1 = sidx + 1 < s1 ? __ldg(a.seg_w + (int64_t)(sidx + 1) * 32 + lane) : Real(0);
+        };
         if (s < s1) {
-            seg_params(s, wN, srcN);
-            prefetch_pass<Real, MM>(up, Lp, srcN, lv, fd);
+            if constexpr (PAIR) {
+                seg_params_pair(s);
+                if (band_is_sw(__ldg(a.seg_band + s)))
+                    prefetch_pair_pass<MM>(up, Lp, srcN, lv, fd2);
+                else
+                    prefetch_pass<Real, MM>(up, Lp, srcN, lv, fd);
+            } else {
+                seg_params(s, wN, srcN);
+                prefetch_pass<Real, MM>(up, Lp, srcN, lv, fd);
+            }
         }
         // Parameters of a (warp, band) run -- band, first chain, band length, sum of the nu-weights -- come from global
         // memory through two dependent loads; those of the NEXT run are requested when a run starts and arrive
@@ -1558,6 +1778,59 @@ __global__ void __launch_bounds__(variant_threads<Real>(V), 1) flux_kernel(const
                 bacc_up[L - 1] += bnd_up;
                 bacc_dn[0] += bnd_dn;
             }
+            if constexpr (PAIR) {
+                // The first pass of the NEXT run is fed at this run's end, by its kind (rj is the next run's band by now).
+                auto feed_next_run = [&](bool up_next) {
+                    if (e >= s1) return;
+                    if (band_is_sw(rj))
+                        prefetch_pair_pass<MM>(up_next, Lp, srcN, lv, fd2);
+                    else
+                        prefetch_pass<Real, MM>(up_next, Lp, srcN, lv, fd);
+                };
+                if (lw) {
+                    Real wR = Real(0);
+                    for (; s < e; ++s) {
+                        const Real wF = wN;
+                        const void *src_lane = srcN;
+                        if (s + 1 < s1) seg_params_pair(s + 1);
+                        const void *nxt = s + 1 < e ? srcN : nullptr;
+                        if (up)
+                            sweep_pass<Real, MM, true, true, true, V>(lane, nl, Lp, wF, wR, bg, src_lane, nxt, fd, lv, tst, bacc_up, coef + 2 * Lp, coef + 3 * Lp, xaux);
+                        else
+                            sweep_pass<Real, MM, true, false, true, V>(lane, nl, Lp, wF, wR, bs, src_lane, nxt, fd, lv, tst, bacc_dn + 1, coef, coef + Lp, xaux);
+                        wR = wF;
+                        up = !up;
+                    }
+                    feed_next_run(!up);
+                    if (up)
+                        sweep_pass<Real, MM, true, true, false, V>(lane, nl, Lp, Real(0), wR, bg, nullptr, nullptr, fd, lv, tst, bacc_up, coef + 2 * Lp, coef + 3 * Lp, xaux);
+                    else
+                        sweep_pass<Real, MM, true, false, false, V>(lane, nl, Lp, Real(0), wR, bs, nullptr, nullptr, fd, lv, tst, bacc_dn + 1, coef, coef + Lp, xaux);
+                    up = !up;
+                } else {
+                    f2 wR = f2_set(0.f);
+                    while (s < e) {
+                        const f2 wF = make_float2(wN, s + 1 < e ? wN1 : 0.f);
+                        const void *src_lane = srcN;
+                        const int sn = min(s + 2, e);
+                        if (sn < s1) seg_params_pair(sn);
+                        const void *nxt = sn < e ? srcN : nullptr;
+                        if (up)
+                            sw_fresh_pair_pass<MM, true, V>(Lp, wF, wR, bg, src_lane, nxt, fd2, lv, tst.taddr, ra);
+                        else
+                            sw_fresh_pair_pass<MM, false, V>(Lp, wF, wR, bs, src_lane, nxt, fd2, lv, tst.taddr, ra);
+                        wR = wF;
+                        up = !up;
+                        s = sn;
+                    }
+                    feed_next_run(!up);
+                    if (up)
+                        sw_replay_pair_pass<true, (V & kVarSmallSt) != 0>(Lp, wR, bg, tst.taddr, ra);
+                    else
+                        sw_replay_pair_pass<false, (V & kVarSmallSt) != 0>(Lp, wR, bs, tst.taddr, ra);
+                    up = !up;
+                }
+            } else {
             Real wR = Real(0);
             for (; s < e; ++s) {
                 const Real wF = wN;
@@ -1571,6 +1844,7 @@ __global__ void __launch_bounds__(variant_threads<Real>(V), 1) flux_kernel(const
             dispatch_pass<Real, MM, false, V>(lw, up, lane, nl, Lp, Real(0), wR, bs, bg, nullptr, s < s1 ? srcN : nullptr, fd, lv,
                                               tst, bacc_up, bacc_dn, coef, xaux, ra);
             up = !up;
+            }
             // ---- partial band sums of this (warp, band) run -> scratch slot ---------------------------
             __syncwarp();
             double *o = a.scratch + ((region * a.n_slots + slot) * 2) * (int64_t)L;
@@ -1579,8 +1853,10 @@ __global__ void __launch_bounds__(variant_threads<Real>(V), 1) flux_kernel(const
                 // (padding layers >= nl hold junk), a downward layer k interface k + 1.  Slot of layer k, class c:
                 // FP64 (k / 8) * 32 + (k & 3) + 4 c, .x for k % 8 < 4, .y otherwise; FP32 (k / 8) * 32 + (k % 8) / 2 + 4 c,
                 // .x for even k; classes added in order.
-                auto pslot = [](int k) { return (k >> 3) * 32 + (sizeof(Real) == 8 ? (k & 3) : ((k & 7) >> 1)); };
-                auto phigh = [](int k) { return sizeof(Real) == 8 ? (k & 4) != 0 : (k & 1) != 0; };
+                // (kVarPair parks two words per value, so its classes are laid out like FP64's)
+                constexpr bool WIDE = sizeof(Real) == 8 || PAIR;
+                auto pslot = [](int k) { return (k >> 3) * 32 + (WIDE ? (k & 3) : ((k & 7) >> 1)); };
+                auto phigh = [](int k) { return WIDE ? (k & 4) != 0 : (k & 1) != 0; };
                 for (int i = lane; i < L; i += 32) {
                     double su = bacc_up[i], sd = bacc_dn[i];
                     if (!lw) {

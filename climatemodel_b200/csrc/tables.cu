@@ -119,14 +119,15 @@ __global__ void level_table_kernel(const double *__restrict__ k, int n_T, int64_
 // Level table in segment space: KS[row][c] = KL[row][seg_bin[c]], row = (molecule, level, table T).
 template <typename Real>
 __global__ void segment_table_kernel(const Real *__restrict__ KL, int64_t n_rows, int64_t pitch,
-                                     const int32_t *__restrict__ seg_bin, int64_t spitch, Real *__restrict__ KS) {
+                                     const int32_t *__restrict__ seg_bin, int64_t n_chains, int64_t spitch,
+                                     Real *__restrict__ KS) {
     const int64_t c = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-    if (c >= spitch) return;
+    if (c >= n_chains) return;           // (the row's padding beyond the last segment stays zero)
     const int32_t n = seg_bin[c];
     for (int64_t row = blockIdx.y; row < n_rows; row += gridDim.y) KS[row * spitch + c] = KL[row * pitch + n];
 }
-template __global__ void segment_table_kernel<double>(const double *, int64_t, int64_t, const int32_t *, int64_t, double *);
-template __global__ void segment_table_kernel<float>(const float *, int64_t, int64_t, const int32_t *, int64_t, float *);
+template __global__ void segment_table_kernel<double>(const double *, int64_t, int64_t, const int32_t *, int64_t, int64_t, double *);
+template __global__ void segment_table_kernel<float>(const float *, int64_t, int64_t, const int32_t *, int64_t, int64_t, float *);
 
 template __global__ void level_table_kernel<double>(const double *, int, int64_t, const int32_t *,
                                                     const int32_t *, int, int, int64_t, int64_t,

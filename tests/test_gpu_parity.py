@@ -262,6 +262,28 @@ def test_whole_column_mode_equals_split_mode():
         assert np.array_equal(many[k][:3], many[k][-3:])         # deterministic across CTAs
 
 
+@pytest.mark.parametrize('name', ['two_mol_nz41', 'co2_nz50_earth'])
+def test_fp32_pair_passes_match_single_segment_passes(name, monkeypatch):
+    """FP32 default: a short-wave pass carries two consecutive segments per lane in packed FP32 arithmetic
+    (FFMA2 / FMUL2 / FADD2, 8 warps); CMB200_FLUX_VARIANT=28675 is the same kernel with one segment per pass on 12
+    warps.  Same chains, other summation order of the lanes: a few FP32 ulp of the largest flux apart, in split
+    mode (few columns: parts end inside bands, odd shares) and in whole-column mode."""
+    c = load_case(name)
+    plan = make_plan(c, precision='f32', tables=True)
+    for n_col in (2, 1300):
+        T, T_g, T_tau, albedo, q = batch_inputs(c, n_col, seed=23)
+        monkeypatch.setenv('CMB200_FLUX_VARIANT', '28675')
+        one = plan.flux(T, T_g, T_tau=T_tau, q=q, albedo=albedo)
+        monkeypatch.delenv('CMB200_FLUX_VARIANT', raising=False)
+        two = plan.flux(T, T_g, T_tau=T_tau, q=q, albedo=albedo)
+        for k in ('up', 'down', 'net'):
+            assert np.isfinite(two[k]).all()
+            assert relmax(two[k], one[k]) < 4e-6
+        for i in range(min(n_col, 16)):
+            assert heating_ok(two['heating'][i], one['heating'][i], two['up'][i], two['down'][i], c['bands']['delta'], c['P'],
+                              1e-5, eps=np.finfo(np.float32).eps)
+
+
 @pytest.mark.parametrize('precision', ['f64', 'f32'])
 def test_tensor_memory_tstore_equals_shared_memory_tstore(precision, monkeypatch):
     """CMB200_FLUX_VARIANT=3 keeps the per-lane t-store in tensor memory (LDTM / STTM) and stages the
