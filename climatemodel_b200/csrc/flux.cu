@@ -371,7 +371,7 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     if constexpr ((V & (kVarExpLds | kVarSwDirect)) != 0) {
         if (!p->exp_tab.p) {      // 2^(j/512): exp2l in long double (64-bit significand), rounded once to double
             std::vector<double> tab(kXlN);
-            for (int j = 0; j < kXlN; ++j) tab[j] = (double)exp2l((long double)j / kXlN);
+            for (int j = 0; j < kXlN; ++j) tab[j] = xl_table_entry((double)exp2l((long double)j / kXlN), j);
             CMB_CUDA(p->exp_tab.upload(tab.data(), tab.size()));
         }
         a.exp_tab = p->exp_tab.p;
@@ -807,7 +807,7 @@ extern "C" int cmb200_test_exp_neg_table_host(const double *x, int64_t n, double
     CMB_CUDA(dx.upload(x, n));
     CMB_CUDA(dout.alloc(n));
     std::vector<double> tab(kXlN);
-    for (int j = 0; j < kXlN; ++j) tab[j] = (double)exp2l((long double)j / kXlN);
+    for (int j = 0; j < kXlN; ++j) tab[j] = xl_table_entry((double)exp2l((long double)j / kXlN), j);
     CMB_CUDA(dtab.upload(tab.data(), tab.size()));
     constexpr int V = kVarExpLds | kVarSwDirect;
     const int smem = (int)(xl_window(V) + kXlBytes);

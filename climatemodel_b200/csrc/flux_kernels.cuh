@@ -25,6 +25,7 @@
 // A band run ends with a replay-only pass.  Per-(warp, band) partial sums go to a small global
 // scratch (L2 resident) and are added in a fixed order, so results do not depend on scheduling.
 #pragma once
+#include <cstring>
 #include "internal.cuh"
 #include "tmem.cuh"
 
@@ -113,6 +114,17 @@ struct ExpAux {
     const double *lds;
     unsigned saddr;       // kVarSwDirect: xl_window(V) | (lane & 15) * 8
 };
+__device__ __forceinline__ double xl_scale(double tt, int n);
+// Entry j of the table as the kernels keep it: 2^(j/512), correctly rounded, with j * 2^11 subtracted from the high
+// word (integer arithmetic on the bit pattern; xl_scale adds n * 2^11 back before the value is used as a double).
+inline double xl_table_entry(double two_to_j_over_512, int j) {
+    unsigned long long bits;
+    memcpy(&bits, &two_to_j_over_512, 8);
+    bits -= (unsigned long long)j << (32 + 11);
+    double r;
+    memcpy(&r, &bits, 8);
+    return r;
+}
 // Threads per CTA the kernel is compiled for: 8 warps, or 12 (168 registers) for the FP32 direct passes with one
 // segment per pass, whose t-stores are half as wide (three warps per lane quarter of tensor memory instead of two).
 template <typename Real>
@@ -630,7 +642,7 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
                     for (int u = 0; u < kU; ++u) {
                         nn[u] = __double2loint(tn[u]);
                         tn[u] -= kMagic;
-                        Tj[u] = xaux.lds[(nn[u] & (kXlN - 1)) * kXlCopies];
+                        Tj[u] = xl_scale(xaux.lds[(nn[u] & (kXlN - 1)) * kXlCopies], nn[u]);      // 2^(j/512) 2^n
                     }
                 }
                 if (DO_B) { Bpair(kb, 1, v, knext); park(kb, 2); park(kb, 3); }
@@ -655,10 +667,7 @@ __device__ __forceinline__ void sweep_pass(const int lane, const int nl, const i
                 if (DO_B) { C2(); C3(); }
                 if (DO_A) {
 #pragma unroll
-                    for (int u = 0; u < kU; ++u) {
-                        const double tt = fma(Tj[u], p[u], Tj[u]);
-                        t[u] = __hiloint2double(__double2hiint(tt) + ((nn[u] >> kXlLog) << 20), __double2loint(tt));
-                    }
+                    for (int u = 0; u < kU; ++u) t[u] = fma(Tj[u], p[u], Tj[u]);
                 }
                 if (DO_B) { C4(); C5(); }
             } else if constexpr (F64) {
@@ -983,10 +992,11 @@ __device__ __forceinline__ double xl_lookup(int n, unsigned saddr_lane) {
     return T;
 }
 __device__ __forceinline__ double xl_scale(double tt, int n) {
-    // tt * 2^(n >> 9): the exponent field gets (n & ~511) * 2^11 = (n >> 9) << 20
-    int m, hi;
-    asm("and.b32 %0, %1, 0xfffffe00;" : "=r"(m) : "r"(n));
-    asm("mad.lo.s32 %0, %1, 2048, %2;" : "=r"(hi) : "r"(m), "r"(__double2hiint(tt)));
+    // 2^(j/512) 2^(n >> 9) from table entry j = n & 511.  The exponent field has to gain (n >> 9) << 20 =
+    // n * 2^11 - j * 2^11; the entries are stored with j * 2^11 already taken off their high word
+    // (xl_table_entry), so one multiply-add with the whole n does it -- no masking of n's low bits.
+    int hi;
+    asm("mad.lo.s32 %0, %1, 2048, %2;" : "=r"(hi) : "r"(n), "r"(__double2hiint(tt)));
     return __hiloint2double(hi, __double2loint(tt));
 }
 

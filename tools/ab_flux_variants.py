@@ -1,6 +1,6 @@
 """A/B of the flux kernel variants (CMB200_FLUX_VARIANT, csrc/flux_kernels.cuh) on one GPU.
 
-    python tools/ab_flux_variants.py [--columns 17760] [--variants 0,3,5123] [--reps 5] [--out file.json]
+    python tools/ab_flux_variants.py [--columns 17760] [--variants 0,3,5123,28675,default] [--reps 5] [--out file.json]
 
 Same workload shape as bench.py (100 levels x 10.4k bins, 2 molecules, per-column T / q), a
 column count that is a multiple of the SM count; every variant is timed with CUDA events and its
@@ -21,11 +21,12 @@ sys.path.insert(0, ROOT)
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--columns', type=int, default=17760)
-    ap.add_argument('--variants', default='0,3,5123')
+    ap.add_argument('--variants', default='0,3,5123,28675,default',
+                    help="CMB200_FLUX_VARIANT values; 'default' = unset (a value a precision does not know runs its default)")
     ap.add_argument('--reps', type=int, default=5)
     ap.add_argument('--out', default=None)
     a = ap.parse_args()
-    variants = [int(v) for v in a.variants.split(',')]
+    variants = [v if v == 'default' else int(v) for v in a.variants.split(',')]
 
     import torch
     from climatemodel_b200 import synthetic
@@ -54,7 +55,10 @@ def main():
     def run(plan, label, n, reps, **kw):
         base = None
         for v in variants:
-            os.environ['CMB200_FLUX_VARIANT'] = str(v)
+            if v == 'default':
+                os.environ.pop('CMB200_FLUX_VARIANT', None)
+            else:
+                os.environ['CMB200_FLUX_VARIANT'] = str(v)
             args = [t[:n] if t.dim() < 3 else t[:, :n].contiguous() for t in dcols]
             dT, dTg, dTt, dq, dal = args
 
