@@ -360,6 +360,27 @@ def test_band_sharding_partial_nets_add_up():
     assert relmax(up, full['up']) < 1e-13
 
 
+def test_fp32_pair_passes_on_shards_and_without_segment_table(monkeypatch):
+    """The FP32 pair passes on partial plans: band ranges and wavenumber-segment ranges (shares that start and end
+    inside bands, at odd segment offsets) add up to the whole plan's fluxes within FP32 rounding, and so does the
+    bin-space table (CMB200_SEGMENT_TABLE=0: no pair passes, one segment per pass)."""
+    c = load_case('two_mol_nz41')
+    args = dict(T_tau=c['T_interface_tau'], q=c['q'], albedo=c['albedo'])
+    full = make_plan(c, precision='f32', tables=True).flux(c['T'], c['T_g'], **args)
+    n_seg = int(make_plan(c, precision='f32', tables=True).segments()[1].size)
+    cuts = sorted({0, 1, n_seg // 3, n_seg // 3 + 3, n_seg // 2 + 1, n_seg})
+    net = np.zeros_like(full['net'])
+    for lo, hi in zip(cuts[:-1], cuts[1:]):
+        plan = make_plan(c, precision='f32', tables=True)
+        plan.set_segment_range(lo, hi)
+        net += plan.flux(c['T'], c['T_g'], **args)['net']
+    assert relmax(net, full['net']) < 4e-6
+    monkeypatch.setenv('CMB200_SEGMENT_TABLE', '0')
+    binspace = make_plan(c, precision='f32', tables=True).flux(c['T'], c['T_g'], **args)
+    for k in ('up', 'down', 'net'):
+        assert relmax(binspace[k], full[k]) < 4e-6
+
+
 # ---- size-independent properties at a larger size ----------------------------------------------------
 def test_properties_larger_grid():
     """10k-bin synthetic table, 100 levels, 64 columns: (i) zero absorber => up flux is the
