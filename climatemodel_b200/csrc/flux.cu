@@ -17,6 +17,7 @@ static int sm_count(int device) {
     return n;
 }
 
+#ifndef CMB_FLUX_SLICE_ONLY      // (launches a kernel of tables.cu: main translation unit only)
 static int ensure_tidx(cmb200_plan *p, int64_t n_col, const double *T_tau, const double *T_g,
                        cudaStream_t s) {
     size_t need = (size_t)p->M * n_col * p->L;
@@ -30,6 +31,7 @@ static int ensure_tidx(cmb200_plan *p, int64_t n_col, const double *T_tau, const
     }
     return CMB200_OK;
 }
+#endif
 
 // Relative cost of one pass of the flux kernel, used to balance the warps of a CTA: a long-wave
 // pass carries the emission recurrences, and every (part, band) run ends with a replay-only pass.
@@ -195,6 +197,9 @@ static int flux_variant() {          // -1: the default of the (type, source) at
 
 // The level table regathered into segment space (internal.cuh) for the fused path; CMB200_SEGMENT_TABLE=0
 // keeps the kernel on the bin-space table (A/B), and so does a failed allocation.
+bool ensure_segment_table_f64(cmb200_plan *p, cudaStream_t s);      // defined in the main translation unit (they launch a kernel of tables.cu)
+bool ensure_segment_table_f32(cmb200_plan *p, cudaStream_t s);
+#ifndef CMB_FLUX_SLICE_ONLY
 template <typename Real>
 static bool ensure_segment_table(cmb200_plan *p, cudaStream_t s) {
     const char *e = getenv("CMB200_SEGMENT_TABLE");
@@ -221,11 +226,14 @@ static bool ensure_segment_table(cmb200_plan *p, cudaStream_t s) {
     p->ks_valid = true;
     return true;
 }
+bool ensure_segment_table_f64(cmb200_plan *p, cudaStream_t s) { return ensure_segment_table<double>(p, s); }
+bool ensure_segment_table_f32(cmb200_plan *p, cudaStream_t s) { return ensure_segment_table<float>(p, s); }
+#endif
 
 template <typename Real, int MM, int V>
 static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *Tint, cudaStream_t s) {
     const int L = p->L, Lp = padded_layers(L);
-    const bool seg_space = MM > 0 && ensure_segment_table<Real>(p, s);
+    const bool seg_space = MM > 0 && (std::is_same<Real, double>::value ? ensure_segment_table_f64(p, s) : ensure_segment_table_f32(p, s));
     const int64_t pitch = seg_space ? p->spitch : p->pitch;
     const double span = MM > 0 ? (double)MM * L * p->nT_pad * (double)pitch * sizeof(Real) / 16.0 : (double)L * (double)p->N;
     if (span >= 4294967296.0) {
@@ -412,6 +420,7 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     return CMB200_OK;
 }
 
+#ifndef CMB_FLUX_SLICE_ONLY
 __global__ void exp_neg_test_kernel(const double *__restrict__ x, int64_t n, double *__restrict__ out) {
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i < n) out[i] = exp_neg(x[i]);
@@ -438,6 +447,8 @@ __global__ void exp_neg_table_test_kernel(const double *__restrict__ x, int64_t 
     }
 }
 
+#endif
+
 template <typename Real, int MM>
 static int launch_flux_variant(int variant, cmb200_plan *plan, const cmb200_flux_io *io, const double *Tint, cudaStream_t s) {
     if constexpr (std::is_same<Real, double>::value && (MM == 0 || MM == 2)) {
@@ -461,6 +472,17 @@ static int launch_flux_variant(int variant, cmb200_plan *plan, const cmb200_flux
     return launch_flux<Real, MM, default_variant<Real, MM>()>(plan, io, Tint, s);
 }
 
+// The flux kernels of one (precision, molecule count) as a translation unit of their own (flux_slice.cu), so that
+// the build compiles them in parallel; CMB_FLUX_SLICES (set by build.py) makes this file call them instead of
+// instantiating the kernels here.
+#define CMB_FLUX_SLICE_DECL(NAME) int NAME(int variant, cmb200_plan *plan, const cmb200_flux_io *io, const double *Tint, cudaStream_t s);
+CMB_FLUX_SLICE_DECL(launch_flux_slice_d0) CMB_FLUX_SLICE_DECL(launch_flux_slice_d1) CMB_FLUX_SLICE_DECL(launch_flux_slice_d2)
+CMB_FLUX_SLICE_DECL(launch_flux_slice_d3) CMB_FLUX_SLICE_DECL(launch_flux_slice_d4)
+CMB_FLUX_SLICE_DECL(launch_flux_slice_f0) CMB_FLUX_SLICE_DECL(launch_flux_slice_f1) CMB_FLUX_SLICE_DECL(launch_flux_slice_f2)
+CMB_FLUX_SLICE_DECL(launch_flux_slice_f3) CMB_FLUX_SLICE_DECL(launch_flux_slice_f4)
+#undef CMB_FLUX_SLICE_DECL
+
+#ifndef CMB_FLUX_SLICE_ONLY
 static int validate_flux_io(const cmb200_plan *p, const cmb200_flux_io *io) {
     CMB_CHECK_ARG(p && io, "null pointer");
     CMB_CHECK_ARG(io->n_col >= 0, "negative column count");
@@ -600,8 +622,15 @@ extern "C" int cmb200_flux(cmb200_plan *plan, const cmb200_flux_io *io, void *st
     }
     const int mm = fused ? plan->M : 0;
     const int variant = flux_variant();
+#ifdef CMB_FLUX_SLICES
+#define CMB_FLUX_SLICE_double(M_) launch_flux_slice_d##M_
+#define CMB_FLUX_SLICE_float(M_) launch_flux_slice_f##M_
+#define CMB_FLUX_CASE(REAL, M_) \
+    case M_: return CMB_FLUX_SLICE_##REAL(M_)(variant, plan, io, Tint, s);
+#else
 #define CMB_FLUX_CASE(REAL, M_) \
     case M_: return launch_flux_variant<REAL, M_>(variant, plan, io, Tint, s);
+#endif
 #ifdef CMB_DEV_BUILD      /* kernel development: only the bench shapes, so that a rebuild takes seconds */
     if (plan->precision == CMB200_F64) {
         switch (mm) {
@@ -817,3 +846,7 @@ extern "C" int cmb200_test_exp_neg_table_host(const double *x, int64_t n, double
     CMB_CUDA(cudaMemcpy(out, dout.p, n * sizeof(double), cudaMemcpyDeviceToHost));
     return CMB200_OK;
 }
+#endif  // CMB_FLUX_SLICE_ONLY
+#ifdef CMB_FLUX_SLICE_ONLY
+}  // namespace cmb
+#endif

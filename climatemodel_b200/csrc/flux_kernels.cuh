@@ -246,7 +246,7 @@ struct TStore {
 // Cody-Waite), degree-11 near-minimax polynomial on |r| <= ln2/2 (max rel. error 1.6e-17 before
 // rounding), scaled by 2^n through the exponent field; no special cases beyond the argument clamp.
 // Coefficients sit in constant memory so that each DFMA takes its constant as an operand.
-__constant__ double kExpC[16] = {
+static __constant__ double kExpC[16] = {      // (static: the kernels are instantiated in several translation units)
     2.51100492048186583e-08, 2.76326547225277896e-07, 2.75572408872298695e-06, 2.48014854415613131e-05,
     1.98412698900764028e-04, 1.38888889523528631e-03, 8.33333333331958900e-03, 4.16666666664879531e-02,
     1.66666666666666796e-01, 5.00000000000001887e-01, 1.0, 1.4426950408889634074,
@@ -1965,7 +1965,7 @@ __global__ void __launch_bounds__(variant_threads<Real>(V), 1) flux_kernel(const
 // (loads issued eight at a time, the adds stay sequential) and leaves the band sum in the band's
 // first slot.  flux_net_kernel: one CTA per column, band sums -> net flux (:712-713) -> heating
 // rate (base.py:166-168), as in the fused epilogue.
-__global__ void flux_band_sums_kernel(int L, int B, int band_lo, int n_slots,
+static __global__ void flux_band_sums_kernel(int L, int B, int band_lo, int n_slots,
                                       const int32_t *__restrict__ band_slot0, double *scratch,
                                       double *up, double *down) {
     const int64_t col = blockIdx.x;
@@ -1990,7 +1990,7 @@ __global__ void flux_band_sums_kernel(int L, int B, int band_lo, int n_slots,
     }
 }
 
-__global__ void flux_net_kernel(int L, int band_lo, int band_hi, int n_slots,
+static __global__ void flux_net_kernel(int L, int band_lo, int band_hi, int n_slots,
                                 const int32_t *__restrict__ band_slot0,
                                 const double *__restrict__ band_delta, const double *__restrict__ scratch,
                                 const double *__restrict__ Pint, double g_over_cp, double *net, double *heating) {
@@ -2017,7 +2017,7 @@ __global__ void flux_net_kernel(int L, int band_lo, int band_hi, int n_slots,
 // T_interface = A T (the not-a-knot spline of real_gas.py:634 as a matrix, At = A transposed:
 // [L-1][L]), T_interface[L-1] = T_g (:636).  One warp per (column, 32 interfaces); the sum runs
 // over the layers in order, loads batched by the unrolling.
-__global__ void interface_temperature_kernel(int L, int64_t n_col, const double *__restrict__ At,
+static __global__ void interface_temperature_kernel(int L, int64_t n_col, const double *__restrict__ At,
                                              const double *__restrict__ T,
                                              const double *__restrict__ T_g,
                                              double *__restrict__ Tint) {
