@@ -3,7 +3,7 @@
     python -m climatemodel_b200.csrc.build [--force] [--verbose]
 
 The library is unity.cu plus ten translation units of flux kernel instantiations (flux_slice.cu), compiled in parallel;
-it is rebuilt when any source is newer than the .so.  Called by ``__graft_entry__.build()``.
+it is rebuilt unless the stamp next to the .so matches the sources (content hash), flags and build mode.  Called by ``__graft_entry__.build()``.
 """
 import os
 import shutil
@@ -13,6 +13,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 PKG = os.path.dirname(HERE)
 LIB = os.path.join(PKG, 'libclimatemodel_b200.so')
+STAMP = LIB + '.stamp'
 SOURCES = ['unity.cu', 'plan.cu', 'tables.cu', 'flux.cu', 'flux_slice.cu', 'transmission.cu', 'peaks.cu', 'lines.cu',
            'convect.cu', 'stepper.cu', 'grey.cu', 'noalloc.cu', 'common.cuh', 'internal.cuh', 'flux_kernels.cuh', 'tmem.cuh',
            os.path.join('..', '..', 'include', 'climatemodel_b200.h')]
@@ -28,11 +29,24 @@ def nvcc_path():
     raise RuntimeError('nvcc not found')
 
 
+def source_stamp():
+    """Hash of what the library is built from: every source, the flags, the build mode."""
+    import hashlib
+    h = hashlib.sha256()
+    for name in SOURCES:
+        with open(os.path.join(HERE, name), 'rb') as f:
+            h.update(name.encode() + b'\0' + f.read())
+    h.update(repr((NVCC_FLAGS, os.environ.get('CMB200_EXPERIMENTS', ''), bool(os.environ.get('CMB200_DEV')))).encode())
+    return h.hexdigest()
+
+
 def stale():
-    if not os.path.exists(LIB):
+    """The library is rebuilt unless the stamp written next to it says it was built from exactly these sources in
+    this mode (so a development build, or one older than an edit or a checkout, is never mistaken for the library)."""
+    if not os.path.exists(LIB) or not os.path.exists(STAMP):
         return True
-    t = os.path.getmtime(LIB)
-    return any(os.path.getmtime(os.path.join(HERE, s)) > t for s in SOURCES)
+    with open(STAMP) as f:
+        return f.read().strip() != source_stamp()
 
 
 def run_nvcc(cmd, verbose):
@@ -71,7 +85,11 @@ def build(force=False, verbose=False):
     with ThreadPoolExecutor(max_workers=max(1, min(len(jobs), os.cpu_count() or 1))) as pool:
         list(pool.map(lambda j: run_nvcc(j, verbose), jobs))
     objs = [j[j.index('-o') + 1] for j in jobs]
+    if os.path.exists(STAMP):
+        os.remove(STAMP)
     run_nvcc([nvcc_path(), '-gencode', 'arch=compute_100a,code=sm_100a', '-shared', '-Xcompiler', '-fPIC', '-o', LIB] + objs, verbose)
+    with open(STAMP, 'w') as f:
+        f.write(source_stamp() + '\n')
     return LIB
 
 
