@@ -211,7 +211,7 @@ struct CtaSmem {
         off_qg = b;
         b = up16(b + (size_t)MR * lev_stride * sizeof(Real));
         off_hdp = b;
-        b = up16(b + (size_t)Lp * sizeof(Real));
+        b = up16(b + (size_t)Lp * sizeof(Real) * ((V & 32768) ? 2 : 1));      // kVarPair: + the same times -log2 e
         off_xtab = b;
         if ((V & kVarExpLds) && !(V & kVarSwDirect)) b = up16(b + (size_t)kXlN * kXlCopies * sizeof(double));
         off_bsrc = b;
@@ -1362,12 +1362,12 @@ __device__ __forceinline__ void sw_fresh_pair_pass(const int Lp, const f2 wF, co
         }
         {
             float hd[kU];
-            lds_real8(s_hdp + (unsigned)k0 * 4u, hd);
+            lds_real8(s_hdp + (unsigned)(Lp + k0) * 4u, hd);        // half layer thickness times -log2 e (second half of the array)
 #pragma unroll
             for (int u = 0; u < kU; ++u) {
                 const f2 lo = UP ? In[u] : (u ? In[u - 1] : Ic);
                 const f2 hi = UP ? (u < kU - 1 ? In[u + 1] : Ic) : In[u];
-                x[u] = f2_mul(f2_set(hd[u] * -1.4426950408889634f), f2_add(lo, hi));       // -thickness * log2 e
+                x[u] = f2_mul(f2_set(hd[u]), f2_add(lo, hi));       // -thickness * log2 e
             }
             Ic = UP ? In[0] : In[kU - 1];
         }
@@ -1519,7 +1519,10 @@ __global__ void __launch_bounds__(variant_threads<Real>(V), 1) flux_kernel(const
     Real *coef_cta = a.coefbuf + (size_t)blockIdx.x * a.B * 4 * Lp;
     const LevelView<Real> lv{lev_offdn, lev_offup, lev_qg, lstride, hdp};
 
-    for (int k = tid; k < Lp; k += nthr) hdp[k] = k < nl ? (Real)a.hdP[k] : Real(0);
+    for (int k = tid; k < Lp; k += nthr) {
+        hdp[k] = k < nl ? (Real)a.hdP[k] : Real(0);
+        if constexpr (PAIR) hdp[Lp + k] = hdp[k] * Real(-1.4426950408889634);
+    }
     for (int i = lane; i < n_bacc; i += 32) bacc_up[i] = 0.0;
     // The t-store: the first replay of a run reads it with weight 0, so it has to hold finite numbers.
     __shared__ uint32_t s_tmem_base;
