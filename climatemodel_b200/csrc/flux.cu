@@ -173,9 +173,10 @@ static int variant_warps(int L, int max_smem, int *tmem_cpw, int *tmem_cols) {
 // the default one; further variants are experiments, compiled for FP64 with 0 or 2 molecules only
 // when the build names them (CMB200_EXPERIMENTS="17,21" python -m climatemodel_b200.csrc.build) and
 // selected at run time with CMB200_FLUX_VARIANT (tools/ab_flux_variants.py).
-// Default variant per arithmetic type and optical-depth source: FP32 and the reference FP64 variant keep the
-// round-1 kernel (t-store in tensor memory, staged coefficient rows; bit-identical to the plain kernel 0);
-// FP64 adds the shared-memory exp table and, on the table-fused path, the direct short-wave pass.
+// Default variant per arithmetic type and optical-depth source.  Resident tau: the round-1 kernel (kReferenceVariant:
+// t-store in tensor memory, staged coefficient rows; bit-identical to the plain kernel 0), in FP64 with the shared-memory
+// exp table.  Table-fused path: the direct short-wave passes with the tensor-memory lane sums on top of that, in FP32
+// carrying two segments per pass (kVarPair).
 constexpr int kReferenceVariant = kVarTmem | kVarCoefSmem;
 template <typename Real, int MM>
 constexpr int default_variant() {
@@ -184,11 +185,7 @@ constexpr int default_variant() {
     return MM > 0 ? (kReferenceVariant | kVarExpLds | direct) : (kReferenceVariant | kVarExpLds);
 }
 #ifndef CMB_FLUX_EXPERIMENTS
-#ifdef CMB_DEV_BUILD
 #define CMB_FLUX_EXPERIMENTS(X)
-#else
-#define CMB_FLUX_EXPERIMENTS(X)
-#endif
 #endif
 static int flux_variant() {          // -1: the default of the (type, source) at hand
     const char *e = getenv("CMB200_FLUX_VARIANT");
