@@ -13,6 +13,7 @@ static int sm_count(int device) {
     if (device < 64 && cached[device]) return cached[device];
     int n = 148;
     cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device);
+    if (const char *e = getenv("CMB200_SM_LIMIT")) n = std::max(1, std::min(n, atoi(e)));     // measurement aid: a smaller persistent grid
     if (device < 64) cached[device] = n;
     return n;
 }
