@@ -573,9 +573,9 @@ def run_b200(a):
                'tolerance': 1e-5,
                'kernel_variant': 'FP32: direct short-wave passes carrying two segments per lane in packed FP32 arithmetic (FFMA2 / FMUL2 / '
                                  'FADD2), t-store and lane sums in tensor memory, 8 warps; CMB200_FLUX_VARIANT=28675 one segment per pass on 12 warps',
-               'bound': 'issue slots 46 % used, neither FP32 pipe (fma 21 %, xu 25 %): the short-wave loops pull their 8 table bytes per unit at '
-                        '~0.65 of the measured L2 -> SM stream while they run (0.39 averaged over the launch, roofline.l2), where L2 latency '
-                        'is what the two warps per scheduler wait for; DESIGN.md section 5',
+               'bound': 'issue slots 46 % used, neither FP32 pipe (fma 21 %, xu 25 %) nor the table stream (all table loads served from L1: '
+                        '0.7 % faster): fixed-latency waits -- the XU serialises a block\'s sixteen MUFU.EX2 -- with two warps per scheduler to hide '
+                        'them; DESIGN.md section 5',
                'roofline': {'fp32': {'achieved': f32_flop * u32 / (ms32 * 1e-3) / 1e12, 'peak': peaks['fp32_reg_tflops'],
                                      'unit': 'TFLOP/s', 'frac': f32_flop * u32 / (ms32 * 1e-3) / 1e12 / peaks['fp32_reg_tflops'],
                                      'flop_per_unit': f32_flop},

@@ -317,6 +317,7 @@ static int launch_flux(cmb200_plan *p, const cmb200_flux_io *io, const double *T
     a.N = p->N;
     a.pitch = pitch;
     a.seg_space = seg_space;
+    a.dbg_row0 = getenv("CMB200_DEBUG_ROW0") != nullptr;
     a.n_col = io->n_col;
     a.n_tasks = n_tasks;
     a.geo = p->geo.p;

@@ -65,6 +65,7 @@ struct FluxArgs {
     long long *dbg;            // optional: sweep cycles per warp of CTA 0's first task (CMB200_DEBUG_TIMING)
     int tmem_cols, tmem_cpw;   // TMEM t-store: columns allocated per CTA, columns per warp (V & kVarTmem)
     const double *exp_tab;     // [kXlN] 2^(j/512), correctly rounded (kVarExpLds)
+    int dbg_row0;
     int seg_space;             // KL is the segment-space table (column = segment * 32 + lane), pitch its row length
 };
 
@@ -1625,7 +1626,7 @@ __global__ void __launch_bounds__(variant_threads<Real>(V), 1) flux_kernel(const
         // ---- the column's level tables ---------------------------------------------------------------
         for (int idx = tid; idx < MR * lstride; idx += nthr) {
             const int m = idx / lstride, pos = idx - m * lstride;
-            const int k = pos - kLevShift, kc = min(max(k, 0), L - 1), kcu = min(max(k - 1, 0), L - 1);
+            const int k = pos - kLevShift, kc = a.dbg_row0 ? 0 : min(max(k, 0), L - 1), kcu = a.dbg_row0 ? 0 : min(max(k - 1, 0), L - 1);
             if (FUSED) {
                 const uint8_t *tcol = a.tidx + ((int64_t)m * a.n_col + col) * L;
                 lev_offdn[idx] = (unsigned)(((((int64_t)m * L + kc) * a.nT_pad + tcol[kc]) * a.pitch * sizeof(Real)) >> 4);
