@@ -34,6 +34,8 @@ def main():
     ap.add_argument('--dnu', type=float, default=5.0)
     ap.add_argument('--nz', type=int, default=100)
     ap.add_argument('--no-convection', action='store_true')
+    ap.add_argument('--precision', default='f64', choices=['f64', 'f32'], help='arithmetic of the flux kernel (the stepper stays FP64)')
+    ap.add_argument('--repeat', type=int, default=2, help='runs of the whole ensemble; the last one is reported (the first pays one-time set-up)')
     a = ap.parse_args()
 
     import torch
@@ -67,19 +69,19 @@ def main():
     q[0] = synthetic.co2_mass_ratio(ppmv_all[mine])[:, None]
     q[1] = 0.005 * (P[None, :] / P[-1]) ** 3              # H2O-like, decaying with height
     t = lambda x: torch.tensor(np.ascontiguousarray(x), device=dev)
-    plan = FluxPlan(P, w['nu'], w['bands'], tables=w['tables'], device=local)
-    cols = ColumnStepper(plan, t(T0), t(T_g), q=t(q), T_tau=t(T_tau), albedo=0.3)
-
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    l0 = _lib.launch_count()
-    t0 = time.perf_counter()
-    n_steps = cols.evolve_to_equilibrium(flux_thresh=a.flux_thresh, convective_adjust=not a.no_convection,
-                                         t_end=a.t_end, max_steps=a.max_steps)
-    torch.cuda.synchronize()
-    wall = time.perf_counter() - t0
-    launches = _lib.launch_count() - l0
+    plan = FluxPlan(P, w['nu'], w['bands'], tables=w['tables'], precision=a.precision, device=local)
+    for _ in range(max(1, a.repeat)):
+        cols = ColumnStepper(plan, t(T0), t(T_g), q=t(q), T_tau=t(T_tau), albedo=0.3)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        l0 = _lib.launch_count()
+        t0 = time.perf_counter()
+        n_steps = cols.evolve_to_equilibrium(flux_thresh=a.flux_thresh, convective_adjust=not a.no_convection,
+                                             t_end=a.t_end, max_steps=a.max_steps)
+        torch.cuda.synchronize()
+        wall = time.perf_counter() - t0
+        launches = _lib.launch_count() - l0
 
     out = torch.cat((cols.T, cols.t[:, None], n_steps.to(torch.float64)[:, None],
                      cols.net_flux.abs().amax(dim=1, keepdim=True)), dim=1)          # [n_col, L-1 + 3]
@@ -102,7 +104,7 @@ def main():
                 'config': {'workload': 'RCE CO2-doubling ensemble over latitude (BASELINE configs[4])',
                            'latitudes': a.latitudes, 'members': 2, 'columns': int(n_all), 'levels': int(L),
                            'bins': int(w['nu'].size), 'flux_thresh': a.flux_thresh, 't_end_years': a.t_end,
-                           'convective_adjust': not a.no_convection},
+                           'convective_adjust': not a.no_convection, 'flux_precision': a.precision, 'runs': a.repeat},
                 'wall_s': wall, 'column_steps': int(col_steps), 'max_steps_of_a_column': int(max_steps),
                 'gpu_launches': int(launches),
                 'model_years_mean': float(full[:, L - 1].mean() / (365 * 86400)),
