@@ -327,6 +327,22 @@ def rce_record(torch, plan, w, dev, n_col, n_steps=24):
                                 'one column on one SM; launches are not the limit (a CUDA-graph replay of the whole step measures the same)',
                        'gpu_launches': int(_lib.launch_count() - l0),
                        'dT_lowest_layer_2xCO2_K_mean': float((surf[1::2] - surf[0::2]).mean())}
+    # the same ensemble with the flux kernel in FP32 mode (stepper, convection and equilibrium test stay FP64)
+    from climatemodel_b200.plan import FluxPlan
+    plan32 = FluxPlan(w['P'], w['nu'], w['bands'], tables=w['tables'], precision='f32', device=dev.index or 0)
+    for trial in range(2):
+        ens = ColumnStepper(plan32, t(np.repeat(Tg[:, None], L - 1, axis=1)), t(Tg), q=t(qe),
+                            T_tau=t(np.repeat(Tg[:, None], L, axis=1)), albedo=0.3)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        steps32 = ens.evolve_to_equilibrium(flux_thresh=1e-3, convective_adjust=True, t_end=4.0, max_steps=200000)
+        torch.cuda.synchronize()
+        wall32 = time.perf_counter() - t0
+    surf32 = ens.T[:, -1].cpu().numpy()
+    plan32.close()
+    rec['ensemble']['f32_flux'] = {'wall_s': wall32, 'column_steps': int(steps32.sum()), 'max_steps_of_a_column': int(steps32.max()),
+                                   'dT_lowest_layer_2xCO2_K_mean': float((surf32[1::2] - surf32[0::2]).mean()),
+                                   'lowest_layer_T_max_abs_diff_vs_f64_K': float(np.abs(surf32 - surf).max())}
     return rec
 
 
